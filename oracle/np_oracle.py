@@ -1,0 +1,568 @@
+"""Stand-alone numpy restatement of the pycsou proximal-solver hot path (the parity oracle).
+
+TEST INFRASTRUCTURE ONLY (see ``oracle/__init__.py``): imported by ``tests/``,
+``__graft_entry__.smoke()`` and the CPU-baseline legs of ``bench.py`` -- never by ``pycsou_b200``.
+
+Every function cites the reference ``file:line`` (relative to /root/reference) it restates.  The
+module depends on numpy/scipy only, so it travels to the GPU box where the reference tree does not
+exist.  Pinning: ``tests/test_oracle_doctests.py`` (the reference's own doctest literals) and
+``tests/test_oracle_golden.py`` (fixtures produced by the reference classes themselves through
+``oracle.ref_shim``; generator ``tests/golden/gen_golden.py``).
+
+Deliberate deviations from the reference, each verified equal on the reference's feasible range:
+* ``L21.prox``/``__call__`` are vectorised (the reference loops over groups in Python, Theta(N^2)).
+* No ``deepcopy`` of iterands and no pandas ``DataFrame``: diagnostics are returned as a dict of lists
+  with the reference's column names.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from oracle import pylops_standin as pl
+
+INF = np.inf
+
+
+# --------------------------------------------------------------------------------------------------
+# math/prox.py
+# --------------------------------------------------------------------------------------------------
+def sign(x):
+    """math/prox.py:61-64 -- NB returns conj(x)/|x| (conjugates complex input)."""
+    x = np.asarray(x)
+    y = np.asarray(0 * x)
+    nz = np.abs(x) != 0
+    y[nz] = np.conj(x[nz]) / np.abs(x[nz])
+    return y
+
+
+def soft(x, tau):
+    """math/prox.py:114."""
+    return np.clip(np.abs(x) - tau, a_min=0, a_max=None) * sign(x)
+
+
+def proj_l2_ball(x, radius):
+    """math/prox.py:207-210."""
+    nrm = np.linalg.norm(x)
+    return x if nrm <= radius else radius * x / nrm
+
+
+def proj_linfty_ball(x, radius):
+    """math/prox.py:253-256 (the reference clips in place; the oracle works on a copy)."""
+    y = np.array(x, copy=True)
+    y[y > radius] = radius
+    y[y < -radius] = -radius
+    return y
+
+
+def proj_nonnegative_orthant(x):
+    """math/prox.py:295-297."""
+    y = np.array(np.real(x), copy=True)
+    y[y < 0] = 0
+    return y
+
+
+def proj_segment(x, a=0, b=1):
+    """math/prox.py:340-343."""
+    y = np.array(np.real(x), copy=True)
+    y[y < a] = a
+    y[y > b] = b
+    return y
+
+
+# --------------------------------------------------------------------------------------------------
+# core/functional.py + func/base.py + func/penalty.py + func/loss.py
+# --------------------------------------------------------------------------------------------------
+class Prox:
+    """ProximableFunctional surface (core/functional.py:157-207)."""
+    dim: int
+
+    def __call__(self, x):
+        raise NotImplementedError
+
+    def prox(self, x, tau):
+        raise NotImplementedError
+
+    def fenchel_prox(self, z, sigma):
+        """core/functional.py:207 (Moreau identity)."""
+        return z - sigma * self.prox(z / sigma, 1 / sigma)
+
+    def __rmul__(self, lam):
+        """core/functional.py:244-246 (positive scalars only)."""
+        if not (np.isscalar(lam) and lam > 0):
+            raise NotImplementedError
+        return PostComp(self, lam)
+
+
+class PostComp(Prox):
+    """ProxFuncPostComp, core/functional.py:253-265."""
+
+    def __init__(self, f, scale):
+        self.f, self.scale, self.dim = f, scale, f.dim
+
+    def __call__(self, x):
+        return self.scale * self.f(x)
+
+    def prox(self, x, tau):
+        return self.f.prox(x, tau * self.scale)
+
+
+class PreCompShift(Prox):
+    """ProxFuncPreComp with scale=1, shift=-data: ``ProximableLoss`` (func/loss.py:69; functional.py:298-299)."""
+
+    def __init__(self, f, data):
+        self.f, self.shift, self.dim = f, -np.asarray(data), f.dim
+
+    def __call__(self, x):
+        return self.f(1 * x + self.shift)
+
+    def prox(self, x, tau):
+        return (self.f.prox(1 * x + self.shift, tau * (1 ** 2)) - self.shift) / 1
+
+
+class LpNorm(Prox):
+    """func/base.py:239-240: prox = x - tau * proj_lq_ball(x / tau, radius=1)."""
+    _proj = None
+
+    def __init__(self, dim):
+        self.dim = dim
+
+    def prox(self, x, tau):
+        return x - tau * type(self)._proj(x / tau, radius=1)
+
+
+class L1Norm(LpNorm):
+    """func/penalty.py:194-245."""
+    _proj = staticmethod(proj_linfty_ball)
+
+    def __call__(self, x):
+        return np.sum(np.abs(x))
+
+
+class L2Norm(LpNorm):
+    """func/penalty.py:23-70."""
+    _proj = staticmethod(proj_l2_ball)
+
+    def __call__(self, x):
+        return np.linalg.norm(x)
+
+
+class L21Norm(Prox):
+    """func/penalty.py:480-560, vectorised.  ``groups`` is an arbitrary label array of length dim."""
+
+    def __init__(self, dim, groups):
+        self.dim = dim
+        self.groups = np.asarray(groups).reshape(-1)
+        self.labels, self.inv = np.unique(self.groups, return_inverse=True)
+
+    def _norms(self, x):
+        return np.sqrt(np.bincount(self.inv, weights=np.abs(x) ** 2, minlength=self.labels.size))
+
+    def __call__(self, x):
+        return np.sum(self._norms(x))
+
+    def prox(self, x, tau):
+        with np.errstate(divide='ignore'):
+            scale = np.clip(1 - tau / self._norms(x), a_min=0, a_max=None)  # penalty.py:554
+        return scale[self.inv] * x
+
+
+class TVL21Norm(Prox):
+    """L21 for the TV layout ``groups = tile(arange(N), C)`` (one group per pixel): fast path of L21Norm."""
+
+    def __init__(self, dim, n_groups):
+        self.dim, self.n = dim, n_groups
+
+    def __call__(self, x):
+        return np.sum(np.linalg.norm(np.reshape(x, (-1, self.n)), axis=0))
+
+    def prox(self, x, tau):
+        X = np.reshape(x, (-1, self.n))
+        with np.errstate(divide='ignore'):
+            scale = np.clip(1 - tau / np.linalg.norm(X, axis=0), a_min=0, a_max=None)
+        return (scale[None, :] * X).reshape(-1)
+
+
+class Indicator(Prox):
+    """IndicatorFunctional, func/base.py:140-168."""
+
+    def __init__(self, dim, cond, proj):
+        self.dim, self.cond, self.proj = dim, cond, proj
+
+    def __call__(self, x):
+        return 0 if self.cond(x) else INF
+
+    def prox(self, x, tau):
+        return self.proj(x)
+
+
+def NonNegativeOrthant(dim):
+    """func/penalty.py:610-612."""
+    return Indicator(dim, lambda x: np.all(x >= 0), proj_nonnegative_orthant)
+
+
+def Segment(dim, a=0, b=1):
+    """func/penalty.py:666-668."""
+    return Indicator(dim, lambda x: np.all((x >= a) & (x <= b)), lambda x: proj_segment(x, a=a, b=b))
+
+
+def L2Ball(dim, radius):
+    """func/penalty.py:189-191."""
+    return Indicator(dim, lambda x: np.linalg.norm(x) <= radius, lambda x: proj_l2_ball(x, radius=radius))
+
+
+class NullProx(Prox):
+    """NullProximableFunctional, func/base.py:194-212."""
+
+    def __init__(self, dim):
+        self.dim = dim
+
+    def __call__(self, x):
+        return 0
+
+    def prox(self, x, tau):
+        return x
+
+
+class ProxHStack(Prox):
+    """ProxFuncHStack, func/base.py:80-89 (separable prox over concatenated blocks)."""
+
+    def __init__(self, *fs):
+        self.fs = fs
+        self.sections = np.cumsum([f.dim for f in fs])
+        self.dim = int(self.sections[-1])
+
+    def __call__(self, x):
+        return sum(f(xi) for f, xi in zip(self.fs, np.split(x, self.sections)))
+
+    def prox(self, x, tau):
+        return np.concatenate([f.prox(xi, tau) for f, xi in zip(self.fs, np.split(x, self.sections))], axis=0)
+
+
+class HalfSquaredL2Loss:
+    """``F = (1/2) * SquaredL2Loss(dim, data=y) * G`` (doc/general/examples.rst:37-38).
+
+    gradient follows the reference's chain rule literally (core/map.py:609-610,
+    571-572; func/penalty.py:129-131; linop/base.py:632-633):  G^T( (2 * (G x + (-y))) * 0.5 ).
+    ``G=None`` means no operator (pure denoising).  beta = diff_lipschitz_cst = 0.5 * 2 * ||G||^2
+    (core/map.py:601-605).
+    """
+
+    def __init__(self, data, G=None, G_lipschitz=1.0):
+        self.y, self.G = np.asarray(data), G
+        self.diff_lipschitz_cst = 0.5 * 2 * (G_lipschitz if G is not None else 1.0) * \
+            (G_lipschitz if G is not None else 1.0)
+        self.dim = G.shape[1] if G is not None else self.y.size
+
+    def __call__(self, x):
+        r = (self.G.matvec(x) if self.G is not None else x) + (-self.y)
+        return 0.5 * np.linalg.norm(r) ** 2
+
+    def gradient(self, x):
+        r = (self.G.matvec(x) if self.G is not None else x) + (-self.y)
+        g = (2 * r) * 0.5
+        return self.G.rmatvec(g) if self.G is not None else g
+
+
+class NullDiff:
+    """NullDifferentiableFunctional, func/base.py:171-191."""
+
+    def __init__(self, dim):
+        self.dim, self.diff_lipschitz_cst = dim, 0
+
+    def __call__(self, x):
+        return 0
+
+    def gradient(self, x):
+        return np.zeros(shape=self.dim)
+
+
+# --------------------------------------------------------------------------------------------------
+# linop/sampling.py (own code of the reference, not pylops)
+# --------------------------------------------------------------------------------------------------
+class Masking:
+    """linop/sampling.py:166-196."""
+
+    def __init__(self, size, sampling_bool, dtype=np.float64):
+        self.sampling_bool = np.asarray(sampling_bool).reshape(-1).astype(bool)
+        if self.sampling_bool.size != size:
+            raise ValueError('Invalid size of boolean sampling array.')
+        self.input_size, self.nb_of_samples = size, int(self.sampling_bool.sum())
+        self.shape, self.dtype = (self.nb_of_samples, size), dtype
+
+    def matvec(self, x):
+        return x[self.sampling_bool]
+
+    def rmatvec(self, y):
+        x = np.zeros(shape=self.input_size, dtype=self.dtype)
+        x[self.sampling_bool] = y
+        return x
+
+
+def downsampling_mask(size, factor, shape=None, axis=None):
+    """linop/sampling.py:323-329 (factor normalisation) and 362-391 (compute_downsampling_mask)."""
+    if type(factor) is int:
+        factor = len(shape) * (factor,) if (shape is not None and axis is None) else (factor,)
+    else:
+        factor = tuple(factor)
+    if shape is None:
+        return (np.arange(size) % factor) == 0
+    if len(factor) > 1:
+        mask = True
+        for ax in range(len(shape)):
+            idx = (np.arange(shape[ax]) % factor[ax]).reshape((shape[ax],) + (len(shape) - 1) * (1,))
+            mask = mask * (np.swapaxes(idx, 0, ax) == 0)
+        return np.asarray(mask).reshape(-1)
+    mask = np.swapaxes(np.zeros(shape=shape, dtype=bool), 0, axis)
+    mask[(np.arange(shape[axis]) % factor) == 0, ...] = True
+    return np.swapaxes(mask, 0, axis).reshape(-1)
+
+
+class LinOpVStackOracle:
+    """LinOpVStack, linop/base.py:159-314: concatenated outputs; adjoint splits at cumsum(block sizes) and sums."""
+
+    def __init__(self, *ops):
+        self.ops = ops
+        self.sections = np.cumsum([op.shape[0] for op in ops])
+        self.shape = (int(self.sections[-1]), ops[0].shape[1])
+
+    def matvec(self, x):
+        return np.concatenate([np.asarray(op.matvec(x)).flatten() for op in self.ops], axis=0)
+
+    def rmatvec(self, y):
+        res = 0
+        for op, yi in zip(self.ops, np.split(y, self.sections)):
+            res = res + op.rmatvec(yi)
+        return res
+
+
+class FFT2Ortho:
+    """Unitary 2-D DFT (the reference ships none: linop/transform.py is empty; UnitaryOperator API core/linop.py:574-615)."""
+
+    def __init__(self, shape):
+        self.img_shape = tuple(shape)
+        n = int(np.prod(shape))
+        self.shape = (n, n)
+
+    def matvec(self, x):
+        return np.fft.fft2(np.reshape(x, self.img_shape), norm='ortho').reshape(-1)
+
+    def rmatvec(self, y):
+        return np.fft.ifft2(np.reshape(y, self.img_shape), norm='ortho').reshape(-1)
+
+
+class Comp:
+    """LinOpComp, core/linop.py:540-553 (adjoint reverses the order)."""
+
+    def __init__(self, A, B):
+        self.A, self.B, self.shape = A, B, (A.shape[0], B.shape[1])
+
+    def matvec(self, x):
+        return self.A.matvec(self.B.matvec(x))
+
+    def rmatvec(self, y):
+        return self.B.rmatvec(self.A.rmatvec(y))
+
+
+# --------------------------------------------------------------------------------------------------
+# opt/proxalgs.py + core/solver.py
+# --------------------------------------------------------------------------------------------------
+def pds_step_sizes(beta, K_lipschitz, has_H=True):
+    """opt/proxalgs.py:280-301 (set_step_sizes) and 312-316 (set_momentum_term)."""
+    if beta > 0:
+        if not has_H:
+            tau, sigma = 2 / beta, 0
+        else:
+            L = K_lipschitz
+            tau = sigma = (1 / L ** 2) * ((-beta / 4) + np.sqrt((beta ** 2 / 16) + L ** 2))
+        rho = 0.9
+    else:
+        if not has_H:
+            tau, sigma = 1, 0
+        else:
+            tau = sigma = 1 / K_lipschitz
+        rho = 1
+    return tau, sigma, rho
+
+
+def _rel_improvement(old, new):
+    """opt/proxalgs.py:372-377."""
+    n = np.linalg.norm(old)
+    return INF if n == 0 else np.linalg.norm(old - new) / n
+
+
+def pds_update(x, z, F, G, H, K, tau, sigma, rho):
+    """One Condat-Vu update, opt/proxalgs.py:343-355.  ``H is None`` <=> ``_H False`` (z untouched)."""
+    Kadj_z = K.rmatvec(z) if H is not None else np.zeros(shape=x.size)  # NullOperator.adjoint linop/base.py:615
+    x_temp = G.prox(x - tau * F.gradient(x) - tau * Kadj_z, tau=tau)
+    if H is not None:
+        u = 2 * x_temp - x
+        z_temp = H.fenchel_prox(z + sigma * K.matvec(u), sigma=sigma)
+        z = rho * z_temp + (1 - rho) * z
+    x = rho * x_temp + (1 - rho) * x
+    return x, z
+
+
+def pds_iterate(dim, F=None, G=None, H=None, K=None, tau=None, sigma=None, rho=None, x0=None, z0=None,
+                max_iter=500, min_iter=10, accuracy_threshold=1e-3, K_lipschitz=None, beta=None,
+                callback=None):
+    """PrimalDualSplitting(...).iterate(): opt/proxalgs.py:126-244, 343-394 + core/solver.py:55-76.
+
+    Returns (x, z, diagnostics, n_updates).  ``K`` is any object with matvec/rmatvec (``None`` with an
+    ``H`` means identity, proxalgs.py:203-205).
+    """
+    F = NullDiff(dim) if F is None else F
+    G = NullProx(dim) if G is None else G
+    beta = F.diff_lipschitz_cst if beta is None else beta
+    if H is not None and K is None:
+        K, K_lipschitz = _Identity(H.dim), 1
+    if tau is not None and sigma is not None:
+        pass
+    elif tau is not None:
+        sigma = tau
+    elif sigma is not None:
+        tau = sigma
+    else:
+        if H is not None and K_lipschitz is None:
+            raise ValueError('Please compute the Lipschitz constant of the linear operator K')
+        tau, sigma, _ = pds_step_sizes(beta, K_lipschitz if H is not None else 0, has_H=H is not None)
+    if rho is None:
+        rho = 0.9 if beta > 0 else 1
+    x = np.zeros(shape=(dim,), dtype=float) if x0 is None else np.asarray(x0)          # proxalgs.py:327
+    z = (None if H is None else np.zeros(shape=(H.dim,), dtype=float)) if z0 is None else np.asarray(z0)
+    cols = ['Iter', 'Relative Improvement (primal variable)'] + \
+        (['Relative Improvement (dual variable)'] if H is not None else [])
+    diag = {c: [] for c in cols}
+    it = 0
+
+    def metric():  # proxalgs.py:360-364
+        return INF if it == 0 else diag[cols[1]][it - 1]
+
+    while ((it <= max_iter) and (metric() > accuracy_threshold)) or (it <= min_iter):  # solver.py:65-66
+        x_old, z_old = x, z
+        x, z = pds_update(x, z, F, G, H, K, tau, sigma, rho)
+        diag['Iter'].append(it)
+        diag[cols[1]].append(_rel_improvement(x_old, x))
+        if H is not None:
+            diag[cols[2]].append(_rel_improvement(z_old, z))
+        if callback is not None:
+            callback(it, x, z)
+        it += 1
+    return x, z, diag, it
+
+
+class _Identity:
+    def __init__(self, n):
+        self.shape = (n, n)
+
+    def matvec(self, x):
+        return 1.0 * x
+
+    def rmatvec(self, y):
+        return 1.0 * y
+
+
+def apgd_iterate(dim, F=None, G=None, tau=None, acceleration='CD', beta=None, x0=None, max_iter=500, min_iter=10,
+                 accuracy_threshold=1e-3, d=75., callback=None):
+    """AcceleratedProximalGradientDescent(...).iterate(): opt/proxalgs.py:485-622 + core/solver.py:55-76.
+
+    Returns (x, past_aux, past_t, diagnostics, n_updates).
+    """
+    F = NullDiff(dim) if F is None else F
+    G = NullProx(dim) if G is None else G
+    beta = F.diff_lipschitz_cst if beta is None else beta
+    tau = 1 / beta if tau is None else tau                               # proxalgs.py:573
+    x = np.zeros(shape=(dim,), dtype=float) if x0 is None else np.asarray(x0)
+    x_old, t_old = 0 * x, 1                                              # proxalgs.py:557
+    diag = {'Iter': [], 'Relative Improvement': []}
+    it = 0
+
+    def metric():
+        return INF if it == 0 else diag['Relative Improvement'][it - 1]
+
+    while ((it <= max_iter) and (metric() > accuracy_threshold)) or (it <= min_iter):
+        x_prev = x
+        x_temp = G.prox(x - tau * F.gradient(x), tau=tau)                # proxalgs.py:591
+        if acceleration == 'BT':
+            t = (1 + np.sqrt(1 + 4 * t_old ** 2)) / 2
+        elif acceleration == 'CD':
+            t = (it + d) / d
+        else:
+            t = t_old = 1
+        a = (t_old - 1) / t
+        x = x_temp + a * (x_temp - x_old)                                # proxalgs.py:599
+        x_old, t_old = x_temp, t
+        diag['Iter'].append(it)
+        diag['Relative Improvement'].append(_rel_improvement(x_prev, x))
+        if callback is not None:
+            callback(it, x, x_temp)
+        it += 1
+    return x, x_old, t_old, diag, it
+
+
+# --------------------------------------------------------------------------------------------------
+# operator factories with the reference's defaults (linop/diff.py, linop/conv.py, linop/sampling.py)
+# --------------------------------------------------------------------------------------------------
+def FirstDerivative(size, shape=None, axis=0, step=1.0, edge=True, dtype='float64', kind='forward'):
+    """linop/diff.py:24-130 (defaults: kind='forward', edge=True)."""
+    return pl.FirstDerivative(N=size, dims=shape, dir=axis, sampling=step, edge=edge, dtype=dtype, kind=kind)
+
+
+def SecondDerivative(size, shape=None, axis=0, step=1.0, edge=True, dtype='float64'):
+    """linop/diff.py:133-219."""
+    return pl.SecondDerivative(N=size, dims=shape, dir=axis, sampling=step, edge=edge, dtype=dtype)
+
+
+def Gradient(shape, step=1., edge=True, dtype='float64', kind='centered'):
+    """linop/diff.py:777-882 (defaults: kind='centered', edge=True)."""
+    return pl.Gradient(dims=shape, sampling=step, edge=edge, dtype=dtype, kind=kind)
+
+
+def Laplacian(shape, weights=(1, 1), step=1., edge=True, dtype='float64'):
+    """linop/diff.py:885-957."""
+    if np.isscalar(step):
+        step = [step] * len(shape)
+    return pl.Laplacian(dims=shape, weights=weights, sampling=step, edge=edge, dtype=dtype)
+
+
+def _offset(n):
+    """linop/conv.py:159-162 / 285-292."""
+    return n // 2 - 1 if n % 2 == 0 else n // 2
+
+
+def Convolve1D(size, filter, reshape_dims=None, axis=0, dtype='float64', method=None):
+    """linop/conv.py:20-164."""
+    filter = np.asarray(filter)
+    return pl.Convolve1D(N=size, h=filter, dims=reshape_dims, dir=axis, dtype=dtype, method=method,
+                         offset=_offset(filter.size))
+
+
+def Convolve2D(size, filter, shape, dtype='float64', method='fft'):
+    """linop/conv.py:167-295."""
+    filter = np.asarray(filter)
+    return pl.Convolve2D(N=size, h=filter, dims=shape, nodir=None, dtype=dtype, method=method,
+                         offset=(_offset(filter.shape[0]), _offset(filter.shape[1])))
+
+
+def SubSampling(size, sampling_indices, shape=None, axis=0, dtype='float64', inplace=True):
+    """linop/sampling.py:25-122."""
+    return pl.Restriction(M=size, iava=sampling_indices, dims=shape, dir=axis, dtype=dtype, inplace=inplace)
+
+
+def DownSampling(size, downsampling_factor, shape=None, axis=None, dtype=np.float64):
+    """linop/sampling.py:199-391."""
+    return Masking(size, downsampling_mask(size, downsampling_factor, shape, axis), dtype=dtype)
+
+
+def power_iteration_lipschitz(op, n_iter=200, seed=0):
+    """Largest singular value by power iteration on op^T op (replaces ARPACK svds, core/linop.py:279-321)."""
+    rng = np.random.default_rng(seed)
+    v = rng.standard_normal(op.shape[1])
+    v /= np.linalg.norm(v)
+    s = 0.0
+    for _ in range(n_iter):
+        w = op.rmatvec(op.matvec(v))
+        s = np.linalg.norm(w)
+        if s == 0:
+            return 0.0
+        v = w / s
+    return float(np.sqrt(s))

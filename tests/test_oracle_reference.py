@@ -1,0 +1,68 @@
+"""Oracle vs the live, unmodified reference (build container only: needs /root/reference)."""
+import warnings
+
+import numpy as np
+import pytest
+
+from oracle import np_oracle as O
+
+pytestmark = pytest.mark.needs_reference
+warnings.filterwarnings('ignore')
+
+
+@pytest.fixture(scope='module')
+def ref():
+    from oracle.ref_shim import load_reference
+    return load_reference()
+
+
+def test_functionals_match_reference(ref):
+    from pycsou.func import penalty as P, loss as L
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal(40)
+    for tau in (0.05, 0.7, 3.0):
+        assert np.array_equal(P.L1Norm(40).prox(x.copy(), tau), O.L1Norm(40).prox(x, tau))
+        assert np.array_equal(P.L2Norm(40).prox(x.copy(), tau), O.L2Norm(40).prox(x, tau))
+        assert np.array_equal((0.3 * P.L1Norm(40)).fenchel_prox(x.copy(), tau), (0.3 * O.L1Norm(40)).fenchel_prox(x, tau))
+        g = np.tile(np.arange(20), 2)
+        assert np.allclose(P.L21Norm(40, g).prox(x.copy(), tau), O.TVL21Norm(40, 20).prox(x, tau), rtol=1e-15, atol=0)
+        assert np.allclose(P.L21Norm(40, g).prox(x.copy(), tau), O.L21Norm(40, g).prox(x, tau), rtol=1e-15, atol=0)
+        y = rng.standard_normal(40)
+        assert np.array_equal(L.L1Loss(40, y).prox(x.copy(), tau), O.PreCompShift(O.L1Norm(40), y).prox(x, tau))
+        assert np.array_equal(L.L2BallLoss(40, y, radius=2.).prox(x.copy(), tau),
+                              O.PreCompShift(O.L2Ball(40, 2.), y).prox(x, tau))
+    assert np.array_equal(P.NonNegativeOrthant(40).prox(x.copy(), 1), O.NonNegativeOrthant(40).prox(x, 1))
+    assert np.array_equal(P.Segment(40, -0.5, 0.2).prox(x.copy(), 1), O.Segment(40, -0.5, 0.2).prox(x, 1))
+
+
+def test_loss_gradient_chain_matches_reference(ref):
+    from pycsou.func.loss import SquaredL2Loss
+    from pycsou.linop.conv import Convolve2D
+    rng = np.random.default_rng(1)
+    shape = (20, 17)
+    h = rng.random((5, 7))
+    y, x = rng.standard_normal(340), rng.standard_normal(340)
+    A = Convolve2D(size=340, filter=h, shape=shape)
+    A.lipschitz_cst = A.diff_lipschitz_cst = 3.0
+    F = (1 / 2) * SquaredL2Loss(dim=340, data=y) * A
+    Fo = O.HalfSquaredL2Loss(y, O.Convolve2D(340, h, shape), G_lipschitz=3.0)
+    assert np.array_equal(F.gradient(x), Fo.gradient(x))
+    assert F.diff_lipschitz_cst == Fo.diff_lipschitz_cst == 9.0
+
+
+def test_step_size_rule_matches_reference(ref):
+    from pycsou.func.loss import SquaredL2Loss
+    from pycsou.func.penalty import L1Norm
+    from pycsou.linop.diff import FirstDerivative
+    from pycsou.opt.proxalgs import PDS
+    D = FirstDerivative(size=30)
+    D.lipschitz_cst = D.diff_lipschitz_cst = 1.7
+    for beta_scale in (1.0, 0.25):
+        F = beta_scale * SquaredL2Loss(dim=30, data=np.ones(30))
+        s = PDS(dim=30, F=F, H=L1Norm(30), K=D, verbose=None)
+        tau, sigma, rho = O.pds_step_sizes(2 * beta_scale, 1.7)
+        assert (s.tau, s.sigma, s.rho) == (tau, sigma, rho)
+    s = PDS(dim=30, F=None, H=L1Norm(30), K=D, verbose=None)
+    assert (s.tau, s.sigma, s.rho) == O.pds_step_sizes(0, 1.7)
+    s = PDS(dim=30, F=SquaredL2Loss(dim=30, data=np.ones(30)), verbose=None)
+    assert (s.tau, s.sigma, s.rho) == O.pds_step_sizes(2, 0, has_H=False)
