@@ -1,0 +1,112 @@
+/* pcsb200.h -- C ABI of libpcsb200.so: B200 (sm_100a) kernels for pycsou's iterative proximal-solver hot path.
+ *
+ * Conventions
+ *  - Plain C types only.  All array arguments are DEVICE pointers owned by the caller (PyTorch allocates them);
+ *    the library never allocates, frees or retains pointers beyond the call.  Workspaces are passed in.
+ *  - Every entry point named <op>_f32 / <op>_f64 exists for float and double; scalars are passed as double.
+ *  - Calls are asynchronous on the cudaStream_t passed as `void* stream`; no synchronisation inside unless stated.
+ *  - Return 0 on success, 1 = bad argument, 2 = CUDA failure; pcs_last_error() (thread-local) describes it.
+ *  - Vectors are flat C-order arrays; operators get the n-D shape.  An n-D array processed along one axis is described
+ *    by the triple (outer, n, inner) = (prod(shape[:axis]), shape[axis], prod(shape[axis+1:])).
+ *  - Stencil / convolution outputs must not alias their inputs (caller ping-pongs); elementwise ops may alias.
+ *
+ * Each block cites the reference interface (file:line under /root/reference) the entry points replace.
+ */
+#ifndef PCSB200_H
+#define PCSB200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+int pcs_version(void);
+const char* pcs_last_error(void);
+int pcs_num_sms(void);
+
+#define PCS_DECL_REAL(name, params) int name##_f32 params; int name##_f64 params;
+
+/* ---- element-wise arithmetic of update_iterand (pycsou/opt/proxalgs.py:348-353, :591-599) ---------------------- */
+PCS_DECL_REAL(pcs_lincomb2, (void* out, double a, const void* x, double b, const void* y, int64_t n, void* stream))
+PCS_DECL_REAL(pcs_lincomb3, (void* out, double a, const void* x, double b, const void* y, double c, const void* z,
+                             int64_t n, void* stream))
+PCS_DECL_REAL(pcs_scale, (void* out, double a, const void* x, int64_t n, void* stream))
+/* DiagonalOperator.__call__/adjoint (pycsou/linop/base.py:569-579) */
+PCS_DECL_REAL(pcs_mul, (void* out, const void* x, const void* y, int64_t n, void* stream))
+
+/* ---- proximal maps ------------------------------------------------------------------------------------------- */
+/* L1Norm.prox = LpNorm.prox with proj_linfty_ball (func/penalty.py:194-245, func/base.py:239-240, math/prox.py:253-256) */
+PCS_DECL_REAL(pcs_prox_l1, (void* out, const void* x, double tau, int64_t n, void* stream))
+/* proj_nonnegative_orthant (math/prox.py:295-297), NonNegativeOrthant.prox (func/penalty.py:563-612) */
+PCS_DECL_REAL(pcs_proj_nonneg, (void* out, const void* x, int64_t n, void* stream))
+/* proj_segment (math/prox.py:340-343), Segment.prox (func/penalty.py:615-668); also proj_linfty_ball */
+PCS_DECL_REAL(pcs_proj_segment, (void* out, const void* x, double a, double b, int64_t n, void* stream))
+/* L21Norm.prox (func/penalty.py:551-557) for groups = tile(arange(n_groups), n_comp); is_complex: interleaved re/im */
+PCS_DECL_REAL(pcs_prox_l21, (void* out, const void* x, double tau, int64_t n_groups, int n_comp, int is_complex,
+                             void* stream))
+/* out = x * f(sumsq): mode 0 L2Norm.prox (func/penalty.py:23-70), mode 1 proj_l2_ball (math/prox.py:207-210),
+ * mode 2 rescale to norm `param` (power iteration, core/linop.py:279-321).  sumsq_f64 = device double holding ||x||^2 */
+PCS_DECL_REAL(pcs_scale_by_norm, (void* out, const void* x, const void* sumsq_f64, double param, int mode, int64_t n,
+                                  void* stream))
+
+/* ---- deterministic reductions (np.linalg.norm in update_diagnostics, opt/proxalgs.py:366-394; functional values) -- */
+int64_t pcs_reduce_workspace_bytes(void);   /* workspace must be zero-initialised once */
+PCS_DECL_REAL(pcs_reduce_sumsq, (const void* x, int64_t n, void* out_f64, void* workspace, void* stream))
+PCS_DECL_REAL(pcs_reduce_sumabs, (const void* x, int64_t n, void* out_f64, void* workspace, void* stream))
+PCS_DECL_REAL(pcs_reduce_diffsumsq, (const void* x, const void* y, int64_t n, void* out_f64, void* workspace,
+                                     void* stream))
+PCS_DECL_REAL(pcs_reduce_dot, (const void* x, const void* y, int64_t n, void* out_f64, void* workspace, void* stream))
+PCS_DECL_REAL(pcs_reduce_minmax, (const void* x, int64_t n, void* out2_f64, void* workspace, void* stream))
+/* L21Norm.__call__ (func/penalty.py:548-549) */
+PCS_DECL_REAL(pcs_reduce_sumgroupnorm, (const void* x, int64_t n_groups, int n_comp, int is_complex, void* out_f64,
+                                        void* workspace, void* stream))
+
+/* ---- finite differences: pylops FirstDerivative/SecondDerivative/Gradient/Laplacian behind
+ *      pycsou/linop/diff.py:128-130, 218-219, 882, 957.  kind: 0 forward, 1 centered, 2 backward ------------------ */
+PCS_DECL_REAL(pcs_firstderiv_fwd, (void* out, const void* x, int64_t outer, int64_t n, int64_t inner, int kind,
+                                   int edge, double step, int accumulate, void* stream))
+PCS_DECL_REAL(pcs_firstderiv_adj, (void* out, const void* x, int64_t outer, int64_t n, int64_t inner, int kind,
+                                   int edge, double step, int accumulate, void* stream))
+PCS_DECL_REAL(pcs_secondderiv_fwd, (void* out, const void* x, int64_t outer, int64_t n, int64_t inner, int kind,
+                                    int edge, double step, int accumulate, void* stream))
+PCS_DECL_REAL(pcs_secondderiv_adj, (void* out, const void* x, int64_t outer, int64_t n, int64_t inner, int kind,
+                                    int edge, double step, int accumulate, void* stream))
+/* 2-D Gradient: out = [d/daxis0 ; d/daxis1] (2*H*W); adjoint: out (H*W) from z (2*H*W) */
+PCS_DECL_REAL(pcs_grad2d_fwd, (void* out, const void* x, int64_t H, int64_t W, int kind, int edge, double step0,
+                               double step1, void* stream))
+PCS_DECL_REAL(pcs_grad2d_adj, (void* out, const void* z, int64_t H, int64_t W, int kind, int edge, double step0,
+                               double step1, void* stream))
+PCS_DECL_REAL(pcs_laplacian2d_fwd, (void* out, const void* x, int64_t H, int64_t W, double w0, double w1, double step0,
+                                    double step1, int edge, void* stream))
+PCS_DECL_REAL(pcs_laplacian2d_adj, (void* out, const void* x, int64_t H, int64_t W, double w0, double w1, double step0,
+                                    double step1, int edge, void* stream))
+
+/* ---- convolution: pylops.signalprocessing.Convolve1D/Convolve2D behind pycsou/linop/conv.py:163, 294.
+ *      forward y[i] = sum_k h[k] x[i+offset-k]; adjoint y[i] = sum_k h[k] x[i+k-offset]; zero "same" boundary ------ */
+PCS_DECL_REAL(pcs_conv1d_fwd, (void* out, const void* x, const void* h, int nh, int offset, int64_t outer, int64_t n,
+                               int64_t inner, void* stream))
+PCS_DECL_REAL(pcs_conv1d_adj, (void* out, const void* x, const void* h, int nh, int offset, int64_t outer, int64_t n,
+                               int64_t inner, void* stream))
+PCS_DECL_REAL(pcs_conv2d_direct_fwd, (void* out, const void* x, const void* h, int kh, int kw, int offset0, int offset1,
+                                      int64_t H, int64_t W, void* stream))
+PCS_DECL_REAL(pcs_conv2d_direct_adj, (void* out, const void* x, const void* h, int kh, int kw, int offset0, int offset1,
+                                      int64_t H, int64_t W, void* stream))
+/* rank-1 filter h = hcol (x) hrow; `sub` (may be NULL) is subtracted from the result: r = A x - y (core/map.py:571-572) */
+PCS_DECL_REAL(pcs_conv2d_sep_fwd, (void* out, const void* x, const void* hcol, const void* hrow, int kh, int kw,
+                                   int offset0, int offset1, const void* sub, int64_t H, int64_t W, void* stream))
+PCS_DECL_REAL(pcs_conv2d_sep_adj, (void* out, const void* x, const void* hcol, const void* hrow, int kh, int kw,
+                                   int offset0, int offset1, const void* sub, int64_t H, int64_t W, void* stream))
+
+/* ---- sampling: Masking/DownSampling (pycsou/linop/sampling.py:190-196, 362-391), SubSampling = pylops.Restriction
+ *      (sampling.py:121).  Elements are opaque 4/8/16-byte words; indices int64, unique for pcs_put ---------------- */
+int pcs_take(void* out, const void* x, const void* idx_i64, int64_t outer, int64_t n, int64_t m, int64_t inner,
+             int elem_bytes, void* stream);
+int pcs_put(void* out, const void* y, const void* idx_i64, int64_t outer, int64_t n, int64_t m, int64_t inner,
+            int elem_bytes, void* stream);
+int64_t pcs_mask_workspace_bytes(int64_t n);
+int pcs_mask_count(const void* mask_u8, int64_t n, void* workspace, void* total_out_i64, void* stream);
+int pcs_mask_indices(const void* mask_u8, int64_t n, const void* workspace, void* idx_out_i64, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCSB200_H */

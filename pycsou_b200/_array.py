@@ -1,0 +1,82 @@
+"""API-edge array handling: numpy / lists / CPU tensors are copied to the device once; results mirror the input kind.
+
+Inside the package everything is a contiguous 1-D CUDA tensor (PyTorch = device memory + streams only).
+"""
+from __future__ import annotations
+
+from numbers import Number
+
+import numpy as np
+import torch
+
+from ._kernels import require_cuda
+
+_NP2T = {np.dtype('float32'): torch.float32, np.dtype('float64'): torch.float64,
+         np.dtype('complex64'): torch.complex64, np.dtype('complex128'): torch.complex128}
+
+
+def torch_dtype(dtype) -> torch.dtype:
+    """Map a numpy-style dtype spec ('float64', np.float32, type, torch dtype, None) to a torch dtype."""
+    if dtype is None:
+        return torch.float64
+    if isinstance(dtype, torch.dtype):
+        return dtype
+    d = np.dtype(dtype)
+    if d.kind in 'iub':
+        return torch.float64
+    try:
+        return _NP2T[d]
+    except KeyError:
+        raise NotImplementedError(f'unsupported dtype {dtype}')
+
+
+def np_dtype(tdtype: torch.dtype):
+    return {v: k for k, v in _NP2T.items()}[tdtype]
+
+
+def is_array(x) -> bool:
+    return isinstance(x, (np.ndarray, torch.Tensor))
+
+
+def device():
+    require_cuda()
+    return torch.device('cuda', torch.cuda.current_device())
+
+
+def to_device(x, dtype: torch.dtype | None = None) -> torch.Tensor:
+    """Contiguous flat CUDA tensor holding ``x`` (one H2D copy for host data, no copy for matching device data)."""
+    if isinstance(x, torch.Tensor):
+        t = x
+        if not t.is_cuda:
+            t = t.to(device(), non_blocking=True)
+    else:
+        a = np.asarray(x)
+        if a.dtype.kind in 'iub':
+            a = a.astype(np.float64)
+        t = torch.from_numpy(np.ascontiguousarray(a)).to(device(), non_blocking=True)
+    if dtype is not None and t.dtype != dtype:
+        if t.is_complex() and not dtype.is_complex:
+            t = t.real            # numpy assignment into a real array drops the imaginary part
+        t = t.to(dtype)
+    t = t.reshape(-1)
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def like_input(result, ref):
+    """Return ``result`` (device tensor or python scalar) in the container kind of ``ref``."""
+    if not isinstance(result, torch.Tensor):
+        return result
+    if isinstance(ref, torch.Tensor):
+        return result if ref.is_cuda else result.cpu()
+    return result.cpu().numpy()
+
+
+def scalar(x) -> float:
+    """Python float from a 0-/1-element device tensor (one D2H sync) or a number."""
+    if isinstance(x, torch.Tensor):
+        return float(x.item())
+    return float(x)
+
+
+def is_number(x) -> bool:
+    return isinstance(x, Number) and not isinstance(x, bool)

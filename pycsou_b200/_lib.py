@@ -1,0 +1,120 @@
+"""ctypes binding of libpcsb200.so (C ABI declared in include/pcsb200.h).
+
+The product path has NO fallback: if the library is missing or a call fails, an exception is raised.
+Signatures are declared here once; ``call(name, *args)`` checks the return code and raises
+``ValueError`` (bad argument) or ``RuntimeError`` (CUDA failure) with ``pcs_last_error()``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libpcsb200.so')
+
+_lib = None
+launch_count = 0   # number of C-ABI compute calls issued (bench.py reports it as gpu_launches evidence)
+
+P, I64, I32, F64 = C.c_void_p, C.c_int64, C.c_int, C.c_double
+
+# name -> argtypes (without dtype suffix); entries listed in REAL get _f32 and _f64 variants.
+REAL = {
+    'pcs_lincomb2': [P, F64, P, F64, P, I64, P],
+    'pcs_lincomb3': [P, F64, P, F64, P, F64, P, I64, P],
+    'pcs_scale': [P, F64, P, I64, P],
+    'pcs_mul': [P, P, P, I64, P],
+    'pcs_prox_l1': [P, P, F64, I64, P],
+    'pcs_proj_nonneg': [P, P, I64, P],
+    'pcs_proj_segment': [P, P, F64, F64, I64, P],
+    'pcs_prox_l21': [P, P, F64, I64, I32, I32, P],
+    'pcs_reduce_sumsq': [P, I64, P, P, P],
+    'pcs_reduce_sumabs': [P, I64, P, P, P],
+    'pcs_reduce_diffsumsq': [P, P, I64, P, P, P],
+    'pcs_reduce_dot': [P, P, I64, P, P, P],
+    'pcs_reduce_minmax': [P, I64, P, P, P],
+    'pcs_reduce_sumgroupnorm': [P, I64, I32, I32, P, P, P],
+    'pcs_scale_by_norm': [P, P, P, F64, I32, I64, P],
+    'pcs_firstderiv_fwd': [P, P, I64, I64, I64, I32, I32, F64, I32, P],
+    'pcs_firstderiv_adj': [P, P, I64, I64, I64, I32, I32, F64, I32, P],
+    'pcs_secondderiv_fwd': [P, P, I64, I64, I64, I32, I32, F64, I32, P],
+    'pcs_secondderiv_adj': [P, P, I64, I64, I64, I32, I32, F64, I32, P],
+    'pcs_grad2d_fwd': [P, P, I64, I64, I32, I32, F64, F64, P],
+    'pcs_grad2d_adj': [P, P, I64, I64, I32, I32, F64, F64, P],
+    'pcs_laplacian2d_fwd': [P, P, I64, I64, F64, F64, F64, F64, I32, P],
+    'pcs_laplacian2d_adj': [P, P, I64, I64, F64, F64, F64, F64, I32, P],
+    'pcs_conv1d_fwd': [P, P, P, I32, I32, I64, I64, I64, P],
+    'pcs_conv1d_adj': [P, P, P, I32, I32, I64, I64, I64, P],
+    'pcs_conv2d_direct_fwd': [P, P, P, I32, I32, I32, I32, I64, I64, P],
+    'pcs_conv2d_direct_adj': [P, P, P, I32, I32, I32, I32, I64, I64, P],
+    'pcs_conv2d_sep_fwd': [P, P, P, P, I32, I32, I32, I32, P, I64, I64, P],
+    'pcs_conv2d_sep_adj': [P, P, P, P, I32, I32, I32, I32, P, I64, I64, P],
+}
+PLAIN = {
+    'pcs_take': ([P, P, P, I64, I64, I64, I64, I32, P], I32),
+    'pcs_put': ([P, P, P, I64, I64, I64, I64, I32, P], I32),
+    'pcs_mask_count': ([P, I64, P, P, P], I32),
+    'pcs_mask_indices': ([P, I64, P, P, P], I32),
+    'pcs_mask_workspace_bytes': ([I64], I64),
+    'pcs_reduce_workspace_bytes': ([], I64),
+    'pcs_version': ([], I32),
+    'pcs_num_sms': ([], I32),
+}
+
+
+def declared_symbols():
+    """All C symbols this binding expects (tests check each is exported by the .so and declared in the header)."""
+    names = list(PLAIN)
+    for base in REAL:
+        names += [base + '_f32', base + '_f64']
+    return names + ['pcs_last_error']
+
+
+def register_real(name, argtypes):
+    REAL[name] = argtypes
+    if _lib is not None:
+        for suf in ('_f32', '_f64'):
+            fn = getattr(_lib, name + suf)
+            fn.argtypes, fn.restype = argtypes, I32
+
+
+def register_plain(name, argtypes, restype=I32):
+    PLAIN[name] = (argtypes, restype)
+    if _lib is not None:
+        fn = getattr(_lib, name)
+        fn.argtypes, fn.restype = argtypes, restype
+
+
+def lib():
+    """Load the shared library (once).  Raises if it has not been built: there is no CPU fallback."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f'{LIB_PATH} not found: build it with `python -m pycsou_b200._build` '
+                               '(pycsou_b200 has no CPU fallback)')
+        L = C.CDLL(LIB_PATH)
+        for base, argtypes in REAL.items():
+            for suf in ('_f32', '_f64'):
+                fn = getattr(L, base + suf)
+                fn.argtypes, fn.restype = argtypes, I32
+        for name, (argtypes, restype) in PLAIN.items():
+            fn = getattr(L, name)
+            fn.argtypes, fn.restype = argtypes, restype
+        L.pcs_last_error.argtypes, L.pcs_last_error.restype = [], C.c_char_p
+        _lib = L
+    return _lib
+
+
+def call(name: str, *args):
+    """Invoke a status-returning entry point; raise on failure."""
+    global launch_count
+    rc = getattr(lib(), name)(*args)
+    launch_count += 1
+    if rc != 0:
+        msg = lib().pcs_last_error().decode(errors='replace')
+        if rc == 1:
+            raise ValueError(msg)
+        raise RuntimeError(msg)
+
+
+def call_plain(name: str, *args):
+    return getattr(lib(), name)(*args)

@@ -1,0 +1,254 @@
+// libpcsb200: compact-filter convolution / correlation with zero "same" boundaries (sm_100a).
+//
+// Replaces pylops.signalprocessing.Convolve1D / Convolve2D -> scipy.signal.convolve / correlate reached from
+// pycsou/linop/conv.py:163, 294.  Semantics (oracle/pylops_standin.py):
+//   forward  y[i] = sum_k h[k] x[i + off - k]        (filter centred at `off`, zero extension)
+//   adjoint  y[i] = sum_k h[k] x[i + k - off]        (correlation = exact transpose)
+// 2-D: the same along both axes.  Three kernels:
+//   conv1d       one axis of an (outer, n, inner) view; taps in shared memory, inputs through L1.
+//   conv2d dir.  dense kh x kw filter, shared-memory tile with halo, 4 outputs per thread.
+//   conv2d sep.  rank-1 filter (h = hcol (x) hrow): row pass and column pass through one shared-memory tile;
+//                optional fused "- y" (residual r = A x - y of the data term).
+#include "pcs_common.cuh"
+
+using namespace pcs;
+
+// ------------------------------------------------------------------------------------------------ 1-D
+constexpr int C1_BLOCK = 256;
+
+template <typename T>
+__global__ void __launch_bounds__(C1_BLOCK) conv1d_kernel(T* __restrict__ out, const T* __restrict__ x,
+                                                          const T* __restrict__ h, int nh, int off, int sgn,
+                                                          int64_t outer, int64_t n, int64_t inner) {
+    extern __shared__ unsigned char smem_raw[];
+    T* taps = reinterpret_cast<T*>(smem_raw);
+    for (int k = threadIdx.x; k < nh; k += C1_BLOCK) taps[k] = h[k];
+    __syncthreads();
+    const int64_t total = outer * n * inner, stride = (int64_t)gridDim.x * C1_BLOCK;
+    for (int64_t f = (int64_t)blockIdx.x * C1_BLOCK + threadIdx.x; f < total; f += stride) {
+        const int64_t i = (f / inner) % n;
+        // position of tap k: i + sgn*(k - off); valid k range so that 0 <= pos < n
+        int k_lo, k_hi;
+        if (sgn > 0) {
+            k_lo = (int)tmax<int64_t>(0, off - i);
+            k_hi = (int)tmin<int64_t>(nh - 1, n - 1 - i + off);
+        } else {
+            k_lo = (int)tmax<int64_t>(0, i + off - (n - 1));
+            k_hi = (int)tmin<int64_t>(nh - 1, i + off);
+        }
+        T acc = T(0);
+        const T* base = x + f + (int64_t)sgn * (k_lo - off) * inner;
+        const int64_t step = (int64_t)sgn * inner;
+        for (int k = k_lo; k <= k_hi; ++k, base += step) acc += taps[k] * base[0];
+        out[f] = acc;
+    }
+}
+
+template <typename T>
+static int conv1d_launch(T* out, const T* x, const T* h, int nh, int off, int sgn, int64_t outer, int64_t n,
+                         int64_t inner, cudaStream_t s, const char* what) {
+    PCS_REQUIRE(outer >= 0 && n >= 0 && inner >= 0 && nh >= 1, "%s: bad dimensions", what);
+    PCS_REQUIRE(off >= 0 && off < nh, "%s: offset must satisfy 0 <= offset < filter size", what);
+    PCS_REQUIRE((size_t)nh * sizeof(T) <= 48 * 1024, "%s: filter too long for the direct kernel (%d taps)", what, nh);
+    const int64_t total = outer * n * inner;
+    if (total == 0) return PCS_OK;
+    PCS_REQUIRE(out && x && h && out != x, "%s: null or aliased pointer", what);
+    conv1d_kernel<T><<<grid_for(total, C1_BLOCK, 8), C1_BLOCK, nh * sizeof(T), s>>>(out, x, h, nh, off, sgn, outer, n,
+                                                                                  inner);
+    return check_launch(what);
+}
+#define C1_PARAMS                                                                                               \
+    (void* out, const void* x, const void* h, int nh, int offset, int64_t outer, int64_t n, int64_t inner, void* stream)
+template <typename T>
+static int pcs_conv1d_fwd_impl(T* o, const T* x, const T* h, int nh, int off, int64_t a, int64_t n, int64_t b,
+                               cudaStream_t s) {
+    return conv1d_launch<T>(o, x, h, nh, off, -1, a, n, b, s, "pcs_conv1d_fwd");
+}
+PCS_EXPORT_REAL(pcs_conv1d_fwd, C1_PARAMS,
+                ((T*)out, (const T*)x, (const T*)h, nh, offset, outer, n, inner, (cudaStream_t)stream))
+template <typename T>
+static int pcs_conv1d_adj_impl(T* o, const T* x, const T* h, int nh, int off, int64_t a, int64_t n, int64_t b,
+                               cudaStream_t s) {
+    return conv1d_launch<T>(o, x, h, nh, off, +1, a, n, b, s, "pcs_conv1d_adj");
+}
+PCS_EXPORT_REAL(pcs_conv1d_adj, C1_PARAMS,
+                ((T*)out, (const T*)x, (const T*)h, nh, offset, outer, n, inner, (cudaStream_t)stream))
+
+// ------------------------------------------------------------------------------------------------ 2-D tiles
+constexpr int C2_TW = 64;       // tile width  (columns)
+constexpr int C2_TH = 32;       // tile height (rows)
+constexpr int C2_BX = 64, C2_BY = 4;   // 256 threads; each thread owns C2_TH / C2_BY = 8 rows of one column
+constexpr int C2_RPT = C2_TH / C2_BY;
+constexpr size_t C2_SMEM_LIMIT = 200 * 1024;
+
+// Load the input tile with its halo; (r0,c0) = image coordinates of smem (0,0).  Outside the image -> 0.
+template <typename T>
+__device__ __forceinline__ void load_tile(T* sm, int sh, int sw, const T* __restrict__ x, int64_t H, int64_t W,
+                                          int64_t r0, int64_t c0) {
+    const int tid = threadIdx.y * C2_BX + threadIdx.x;
+    for (int e = tid; e < sh * sw; e += C2_BX * C2_BY) {
+        const int lr = e / sw, lc = e - lr * sw;
+        const int64_t r = r0 + lr, c = c0 + lc;
+        sm[e] = (r >= 0 && r < H && c >= 0 && c < W) ? x[r * W + c] : T(0);
+    }
+}
+
+// dense filter.  sgn = -1: convolution (forward), +1: correlation (adjoint).
+template <typename T>
+__global__ void __launch_bounds__(C2_BX * C2_BY) conv2d_direct_kernel(T* __restrict__ out, const T* __restrict__ x,
+                                                                      const T* __restrict__ h, int kh, int kw,
+                                                                      int off0, int off1, int sgn, int64_t H,
+                                                                      int64_t W) {
+    extern __shared__ unsigned char smem_raw[];
+    T* taps = reinterpret_cast<T*>(smem_raw);
+    T* tile = taps + kh * kw;
+    const int sh = C2_TH + kh - 1, sw = C2_TW + kw - 1;
+    const int tid = threadIdx.y * C2_BX + threadIdx.x;
+    // store taps in "correlation order": out[r,c] = sum_{a,b} g[a,b] tile[r+a, c+b]
+    for (int e = tid; e < kh * kw; e += C2_BX * C2_BY) {
+        const int a = e / kw, b = e - a * kw;
+        taps[e] = (sgn > 0) ? h[e] : h[(kh - 1 - a) * kw + (kw - 1 - b)];
+    }
+    const int ca = (sgn > 0) ? off0 : kh - 1 - off0, cb = (sgn > 0) ? off1 : kw - 1 - off1;
+    const int64_t R0 = (int64_t)blockIdx.y * C2_TH, C0 = (int64_t)blockIdx.x * C2_TW;
+    load_tile<T>(tile, sh, sw, x, H, W, R0 - ca, C0 - cb);
+    __syncthreads();
+    T acc[C2_RPT];
+#pragma unroll
+    for (int j = 0; j < C2_RPT; ++j) acc[j] = T(0);
+    const int lc = threadIdx.x;
+    for (int a = 0; a < kh; ++a) {
+        for (int b = 0; b < kw; ++b) {
+            const T g = taps[a * kw + b];
+#pragma unroll
+            for (int j = 0; j < C2_RPT; ++j) acc[j] += g * tile[(threadIdx.y + j * C2_BY + a) * sw + lc + b];
+        }
+    }
+    const int64_t c = C0 + lc;
+    if (c < W) {
+#pragma unroll
+        for (int j = 0; j < C2_RPT; ++j) {
+            const int64_t r = R0 + threadIdx.y + j * C2_BY;
+            if (r < H) out[r * W + c] = acc[j];
+        }
+    }
+}
+
+template <typename T>
+static int conv2d_direct_launch(T* out, const T* x, const T* h, int kh, int kw, int off0, int off1, int sgn, int64_t H,
+                                int64_t W, cudaStream_t s, const char* what) {
+    PCS_REQUIRE(H >= 0 && W >= 0 && kh >= 1 && kw >= 1, "%s: bad dimensions", what);
+    PCS_REQUIRE(off0 >= 0 && off0 < kh && off1 >= 0 && off1 < kw, "%s: offset outside the filter", what);
+    if (H * W == 0) return PCS_OK;
+    PCS_REQUIRE(out && x && h && out != x, "%s: null or aliased pointer", what);
+    const size_t smem = ((size_t)kh * kw + (size_t)(C2_TH + kh - 1) * (C2_TW + kw - 1)) * sizeof(T);
+    PCS_REQUIRE(smem <= C2_SMEM_LIMIT, "%s: filter %dx%d too large for the direct kernel", what, kh, kw);
+    cudaFuncSetAttribute(conv2d_direct_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C2_SMEM_LIMIT);
+    dim3 grid((unsigned)((W + C2_TW - 1) / C2_TW), (unsigned)((H + C2_TH - 1) / C2_TH));
+    conv2d_direct_kernel<T><<<grid, dim3(C2_BX, C2_BY), smem, s>>>(out, x, h, kh, kw, off0, off1, sgn, H, W);
+    return check_launch(what);
+}
+#define C2D_PARAMS                                                                                             \
+    (void* out, const void* x, const void* h, int kh, int kw, int offset0, int offset1, int64_t H, int64_t W,  \
+     void* stream)
+template <typename T>
+static int pcs_conv2d_direct_fwd_impl(T* o, const T* x, const T* h, int kh, int kw, int o0, int o1, int64_t H,
+                                      int64_t W, cudaStream_t s) {
+    return conv2d_direct_launch<T>(o, x, h, kh, kw, o0, o1, -1, H, W, s, "pcs_conv2d_direct_fwd");
+}
+PCS_EXPORT_REAL(pcs_conv2d_direct_fwd, C2D_PARAMS,
+                ((T*)out, (const T*)x, (const T*)h, kh, kw, offset0, offset1, H, W, (cudaStream_t)stream))
+template <typename T>
+static int pcs_conv2d_direct_adj_impl(T* o, const T* x, const T* h, int kh, int kw, int o0, int o1, int64_t H,
+                                      int64_t W, cudaStream_t s) {
+    return conv2d_direct_launch<T>(o, x, h, kh, kw, o0, o1, +1, H, W, s, "pcs_conv2d_direct_adj");
+}
+PCS_EXPORT_REAL(pcs_conv2d_direct_adj, C2D_PARAMS,
+                ((T*)out, (const T*)x, (const T*)h, kh, kw, offset0, offset1, H, W, (cudaStream_t)stream))
+
+// rank-1 filter h[a,b] = hcol[a] * hrow[b]; out = conv/corr(x) (- sub if sub != nullptr)
+template <typename T>
+__global__ void __launch_bounds__(C2_BX * C2_BY) conv2d_sep_kernel(T* __restrict__ out, const T* __restrict__ x,
+                                                                   const T* __restrict__ hcol,
+                                                                   const T* __restrict__ hrow, int kh, int kw,
+                                                                   int off0, int off1, int sgn,
+                                                                   const T* __restrict__ sub, int64_t H, int64_t W) {
+    extern __shared__ unsigned char smem_raw[];
+    T* tcol = reinterpret_cast<T*>(smem_raw);
+    T* trow = tcol + kh;
+    const int sh = C2_TH + kh - 1, sw = C2_TW + kw - 1;
+    T* tile = trow + kw;              // sh x sw
+    T* mid = tile + sh * sw;          // sh x C2_TW (row pass result)
+    const int tid = threadIdx.y * C2_BX + threadIdx.x;
+    for (int e = tid; e < kh; e += C2_BX * C2_BY) tcol[e] = (sgn > 0) ? hcol[e] : hcol[kh - 1 - e];
+    for (int e = tid; e < kw; e += C2_BX * C2_BY) trow[e] = (sgn > 0) ? hrow[e] : hrow[kw - 1 - e];
+    const int ca = (sgn > 0) ? off0 : kh - 1 - off0, cb = (sgn > 0) ? off1 : kw - 1 - off1;
+    const int64_t R0 = (int64_t)blockIdx.y * C2_TH, C0 = (int64_t)blockIdx.x * C2_TW;
+    load_tile<T>(tile, sh, sw, x, H, W, R0 - ca, C0 - cb);
+    __syncthreads();
+    // row pass: mid[lr, lc] = sum_b trow[b] tile[lr, lc + b]
+    for (int e = tid; e < sh * C2_TW; e += C2_BX * C2_BY) {
+        const int lr = e / C2_TW, lc = e - lr * C2_TW;
+        T acc = T(0);
+        const T* p = tile + lr * sw + lc;
+        for (int b = 0; b < kw; ++b) acc += trow[b] * p[b];
+        mid[e] = acc;
+    }
+    __syncthreads();
+    // column pass with a register window: thread owns C2_RPT consecutive rows of one column
+    const int lc = threadIdx.x, lr0 = threadIdx.y * C2_RPT;
+    T acc[C2_RPT];
+#pragma unroll
+    for (int j = 0; j < C2_RPT; ++j) acc[j] = T(0);
+    for (int a = 0; a < kh + C2_RPT - 1; ++a) {
+        const T v = mid[(lr0 + a) * C2_TW + lc];
+#pragma unroll
+        for (int j = 0; j < C2_RPT; ++j) {
+            const int t = a - j;
+            if (t >= 0 && t < kh) acc[j] += tcol[t] * v;
+        }
+    }
+    const int64_t c = C0 + lc;
+    if (c < W) {
+#pragma unroll
+        for (int j = 0; j < C2_RPT; ++j) {
+            const int64_t r = R0 + lr0 + j;
+            if (r < H) out[r * W + c] = sub ? acc[j] - sub[r * W + c] : acc[j];
+        }
+    }
+}
+
+template <typename T>
+static int conv2d_sep_launch(T* out, const T* x, const T* hcol, const T* hrow, int kh, int kw, int off0, int off1,
+                             int sgn, const T* sub, int64_t H, int64_t W, cudaStream_t s, const char* what) {
+    PCS_REQUIRE(H >= 0 && W >= 0 && kh >= 1 && kw >= 1, "%s: bad dimensions", what);
+    PCS_REQUIRE(off0 >= 0 && off0 < kh && off1 >= 0 && off1 < kw, "%s: offset outside the filter", what);
+    if (H * W == 0) return PCS_OK;
+    PCS_REQUIRE(out && x && hcol && hrow && out != x, "%s: null or aliased pointer", what);
+    const size_t sh = C2_TH + kh - 1, sw = C2_TW + kw - 1;
+    const size_t smem = ((size_t)kh + kw + sh * sw + sh * C2_TW) * sizeof(T);
+    PCS_REQUIRE(smem <= C2_SMEM_LIMIT, "%s: filter %dx%d too large for the separable kernel", what, kh, kw);
+    cudaFuncSetAttribute(conv2d_sep_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C2_SMEM_LIMIT);
+    dim3 grid((unsigned)((W + C2_TW - 1) / C2_TW), (unsigned)((H + C2_TH - 1) / C2_TH));
+    conv2d_sep_kernel<T><<<grid, dim3(C2_BX, C2_BY), smem, s>>>(out, x, hcol, hrow, kh, kw, off0, off1, sgn, sub, H, W);
+    return check_launch(what);
+}
+#define C2S_PARAMS                                                                                              \
+    (void* out, const void* x, const void* hcol, const void* hrow, int kh, int kw, int offset0, int offset1,    \
+     const void* sub, int64_t H, int64_t W, void* stream)
+template <typename T>
+static int pcs_conv2d_sep_fwd_impl(T* o, const T* x, const T* hc, const T* hr, int kh, int kw, int o0, int o1,
+                                   const T* sub, int64_t H, int64_t W, cudaStream_t s) {
+    return conv2d_sep_launch<T>(o, x, hc, hr, kh, kw, o0, o1, -1, sub, H, W, s, "pcs_conv2d_sep_fwd");
+}
+PCS_EXPORT_REAL(pcs_conv2d_sep_fwd, C2S_PARAMS,
+                ((T*)out, (const T*)x, (const T*)hcol, (const T*)hrow, kh, kw, offset0, offset1, (const T*)sub, H, W,
+                 (cudaStream_t)stream))
+template <typename T>
+static int pcs_conv2d_sep_adj_impl(T* o, const T* x, const T* hc, const T* hr, int kh, int kw, int o0, int o1,
+                                   const T* sub, int64_t H, int64_t W, cudaStream_t s) {
+    return conv2d_sep_launch<T>(o, x, hc, hr, kh, kw, o0, o1, +1, sub, H, W, s, "pcs_conv2d_sep_adj");
+}
+PCS_EXPORT_REAL(pcs_conv2d_sep_adj, C2S_PARAMS,
+                ((T*)out, (const T*)x, (const T*)hcol, (const T*)hrow, kh, kw, offset0, offset1, (const T*)sub, H, W,
+                 (cudaStream_t)stream))

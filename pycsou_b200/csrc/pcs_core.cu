@@ -1,0 +1,397 @@
+// libpcsb200: error plumbing, elementwise / proximal kernels and deterministic reductions (sm_100a).
+//
+// Reference rows: a19-a25.  Formulas follow the reference literally where rounding
+// could differ (see pcs_common.cuh: prox_l1, l21_factor).
+#include "pcs_common.cuh"
+#include <stdarg.h>
+#include <string.h>
+
+namespace pcs {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("%s: %s", what, cudaGetErrorString(e));
+        return PCS_ERR_CUDA;
+    }
+    return PCS_OK;
+}
+
+int num_sms() {
+    static thread_local int cached_dev = -1, cached = 148;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (dev != cached_dev) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) cached = n;
+        cached_dev = dev;
+    }
+    return cached;
+}
+
+}  // namespace pcs
+
+using namespace pcs;
+
+extern "C" int pcs_version(void) { return 100; }
+extern "C" const char* pcs_last_error(void) { return pcs::g_err; }
+extern "C" int pcs_num_sms(void) { return pcs::num_sms(); }
+
+// ------------------------------------------------------------------------------------------------ elementwise
+constexpr int EW_BLOCK = 256;
+constexpr int EW_CTAS_PER_SM = 8;
+
+enum EwOp {
+    EW_LINCOMB2,    // out = a*x + b*y
+    EW_LINCOMB3,    // out = a*x + b*y + c*z
+    EW_SCALE,       // out = a*x
+    EW_MUL,         // out = x*y
+    EW_MULCONJ,     // (real: same as MUL)
+    EW_PROX_L1,     // out = x - a*clip(x/a,-1,1)
+    EW_NONNEG,      // out = max(x,0)
+    EW_SEGMENT,     // out = clip(x,a,b)
+    EW_SCALE_DEV,   // out = x * s[0]  (device scalar; used by l2 prox / l2-ball projection)
+};
+
+template <typename T, int OP>
+__device__ __forceinline__ T ew_apply(T x, T y, T z, T a, T b, T c) {
+    if (OP == EW_LINCOMB2) return a * x + b * y;
+    if (OP == EW_LINCOMB3) return a * x + b * y + c * z;
+    if (OP == EW_SCALE) return a * x;
+    if (OP == EW_MUL || OP == EW_MULCONJ) return x * y;
+    if (OP == EW_PROX_L1) return prox_l1<T>(x, a);
+    if (OP == EW_NONNEG) return x < T(0) ? T(0) : x;
+    if (OP == EW_SEGMENT) { T v = x < a ? a : x; return v > b ? b : v; }
+    return x;
+}
+
+template <typename T, int OP, int NIN>
+__global__ void __launch_bounds__(EW_BLOCK) ew_kernel(T* __restrict__ out, const T* __restrict__ x,
+                                                      const T* __restrict__ y, const T* __restrict__ z, T a, T b, T c,
+                                                      int64_t n, int vec_ok) {
+    typedef typename Vec<T>::type V;
+    constexpr int VN = Vec<T>::N;
+    const int64_t tid = (int64_t)blockIdx.x * EW_BLOCK + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * EW_BLOCK;
+    if (vec_ok) {
+        const int64_t nv = n / VN;
+        for (int64_t i = tid; i < nv; i += stride) {
+            V vx = reinterpret_cast<const V*>(x)[i], vy = vx, vz = vx, vo;
+            if (NIN > 1) vy = reinterpret_cast<const V*>(y)[i];
+            if (NIN > 2) vz = reinterpret_cast<const V*>(z)[i];
+            const T* px = reinterpret_cast<const T*>(&vx);
+            const T* py = reinterpret_cast<const T*>(&vy);
+            const T* pz = reinterpret_cast<const T*>(&vz);
+            T* po = reinterpret_cast<T*>(&vo);
+#pragma unroll
+            for (int k = 0; k < VN; ++k) po[k] = ew_apply<T, OP>(px[k], py[k], pz[k], a, b, c);
+            reinterpret_cast<V*>(out)[i] = vo;
+        }
+        for (int64_t i = nv * VN + tid; i < n; i += stride)
+            out[i] = ew_apply<T, OP>(x[i], NIN > 1 ? y[i] : T(0), NIN > 2 ? z[i] : T(0), a, b, c);
+    } else {
+        for (int64_t i = tid; i < n; i += stride)
+            out[i] = ew_apply<T, OP>(x[i], NIN > 1 ? y[i] : T(0), NIN > 2 ? z[i] : T(0), a, b, c);
+    }
+}
+
+static inline int aligned16(const void* p) { return p == nullptr || (((uintptr_t)p) & 15u) == 0; }
+
+template <typename T, int OP, int NIN>
+static int ew_launch(T* out, const T* x, const T* y, const T* z, T a, T b, T c, int64_t n, cudaStream_t s,
+                     const char* what) {
+    PCS_REQUIRE(n >= 0, "%s: negative size", what);
+    if (n == 0) return PCS_OK;
+    PCS_REQUIRE(out && x && (NIN < 2 || y) && (NIN < 3 || z), "%s: null pointer", what);
+    int vec_ok = aligned16(out) && aligned16(x) && aligned16(y) && aligned16(z);
+    int grid = grid_for((n + Vec<T>::N - 1) / Vec<T>::N, EW_BLOCK, EW_CTAS_PER_SM);
+    ew_kernel<T, OP, NIN><<<grid, EW_BLOCK, 0, s>>>(out, x, y, z, a, b, c, n, vec_ok);
+    return check_launch(what);
+}
+
+template <typename T> static int pcs_lincomb2_impl(T* out, T a, const T* x, T b, const T* y, int64_t n, cudaStream_t s) {
+    return ew_launch<T, EW_LINCOMB2, 2>(out, x, y, nullptr, a, b, T(0), n, s, "pcs_lincomb2");
+}
+PCS_EXPORT_REAL(pcs_lincomb2, (void* out, double a, const void* x, double b, const void* y, int64_t n, void* stream),
+                ((T*)out, (T)a, (const T*)x, (T)b, (const T*)y, n, (cudaStream_t)stream))
+
+template <typename T>
+static int pcs_lincomb3_impl(T* out, T a, const T* x, T b, const T* y, T c, const T* z, int64_t n, cudaStream_t s) {
+    return ew_launch<T, EW_LINCOMB3, 3>(out, x, y, z, a, b, c, n, s, "pcs_lincomb3");
+}
+PCS_EXPORT_REAL(pcs_lincomb3,
+                (void* out, double a, const void* x, double b, const void* y, double c, const void* z, int64_t n,
+                 void* stream),
+                ((T*)out, (T)a, (const T*)x, (T)b, (const T*)y, (T)c, (const T*)z, n, (cudaStream_t)stream))
+
+template <typename T> static int pcs_scale_impl(T* out, T a, const T* x, int64_t n, cudaStream_t s) {
+    return ew_launch<T, EW_SCALE, 1>(out, x, nullptr, nullptr, a, T(0), T(0), n, s, "pcs_scale");
+}
+PCS_EXPORT_REAL(pcs_scale, (void* out, double a, const void* x, int64_t n, void* stream),
+                ((T*)out, (T)a, (const T*)x, n, (cudaStream_t)stream))
+
+template <typename T> static int pcs_mul_impl(T* out, const T* x, const T* y, int64_t n, cudaStream_t s) {
+    return ew_launch<T, EW_MUL, 2>(out, x, y, nullptr, T(0), T(0), T(0), n, s, "pcs_mul");
+}
+PCS_EXPORT_REAL(pcs_mul, (void* out, const void* x, const void* y, int64_t n, void* stream),
+                ((T*)out, (const T*)x, (const T*)y, n, (cudaStream_t)stream))
+
+// L1Norm.prox (func/penalty.py:194-245 via func/base.py:239-240)
+template <typename T> static int pcs_prox_l1_impl(T* out, const T* x, T tau, int64_t n, cudaStream_t s) {
+    return ew_launch<T, EW_PROX_L1, 1>(out, x, nullptr, nullptr, tau, T(0), T(0), n, s, "pcs_prox_l1");
+}
+PCS_EXPORT_REAL(pcs_prox_l1, (void* out, const void* x, double tau, int64_t n, void* stream),
+                ((T*)out, (const T*)x, (T)tau, n, (cudaStream_t)stream))
+
+// proj_nonnegative_orthant (math/prox.py:295-297)
+template <typename T> static int pcs_proj_nonneg_impl(T* out, const T* x, int64_t n, cudaStream_t s) {
+    return ew_launch<T, EW_NONNEG, 1>(out, x, nullptr, nullptr, T(0), T(0), T(0), n, s, "pcs_proj_nonneg");
+}
+PCS_EXPORT_REAL(pcs_proj_nonneg, (void* out, const void* x, int64_t n, void* stream),
+                ((T*)out, (const T*)x, n, (cudaStream_t)stream))
+
+// proj_segment (math/prox.py:340-343)
+template <typename T> static int pcs_proj_segment_impl(T* out, const T* x, T a, T b, int64_t n, cudaStream_t s) {
+    return ew_launch<T, EW_SEGMENT, 1>(out, x, nullptr, nullptr, a, b, T(0), n, s, "pcs_proj_segment");
+}
+PCS_EXPORT_REAL(pcs_proj_segment, (void* out, const void* x, double a, double b, int64_t n, void* stream),
+                ((T*)out, (const T*)x, (T)a, (T)b, n, (cudaStream_t)stream))
+
+// ------------------------------------------------------------------------------------------------ L21 prox
+// L21Norm.prox for the "planes" layout groups = tile(arange(G), C): component c of group g is x[c*G + g]
+// (func/penalty.py:551-557).  `cplx` = 1 treats each element as (re,im) pair of T.
+template <typename T, int C>
+__global__ void __launch_bounds__(EW_BLOCK) prox_l21_kernel(T* __restrict__ out, const T* __restrict__ x, T tau,
+                                                            int64_t G, int cplx) {
+    const int64_t stride = (int64_t)gridDim.x * EW_BLOCK;
+    const int64_t e = cplx ? 2 : 1;
+    for (int64_t g = (int64_t)blockIdx.x * EW_BLOCK + threadIdx.x; g < G; g += stride) {
+        T v[C * 2];
+        T ss = T(0);
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            for (int k = 0; k < e; ++k) {
+                v[c * 2 + k] = x[((int64_t)c * G + g) * e + k];
+                ss += v[c * 2 + k] * v[c * 2 + k];
+            }
+        }
+        const T f = l21_factor<T>(tsqrt<T>(ss), tau);
+#pragma unroll
+        for (int c = 0; c < C; ++c)
+            for (int k = 0; k < e; ++k) out[((int64_t)c * G + g) * e + k] = f * v[c * 2 + k];
+    }
+}
+
+template <typename T>
+static int pcs_prox_l21_impl(T* out, const T* x, T tau, int64_t G, int C, int cplx, cudaStream_t s) {
+    PCS_REQUIRE(G >= 0 && C >= 1 && C <= 4, "pcs_prox_l21: need 1 <= n_comp <= 4 (got %d)", C);
+    if (G == 0) return PCS_OK;
+    PCS_REQUIRE(out && x, "pcs_prox_l21: null pointer");
+    int grid = grid_for(G, EW_BLOCK, EW_CTAS_PER_SM);
+    switch (C) {
+        case 1: prox_l21_kernel<T, 1><<<grid, EW_BLOCK, 0, s>>>(out, x, tau, G, cplx); break;
+        case 2: prox_l21_kernel<T, 2><<<grid, EW_BLOCK, 0, s>>>(out, x, tau, G, cplx); break;
+        case 3: prox_l21_kernel<T, 3><<<grid, EW_BLOCK, 0, s>>>(out, x, tau, G, cplx); break;
+        default: prox_l21_kernel<T, 4><<<grid, EW_BLOCK, 0, s>>>(out, x, tau, G, cplx); break;
+    }
+    return check_launch("pcs_prox_l21");
+}
+PCS_EXPORT_REAL(pcs_prox_l21,
+                (void* out, const void* x, double tau, int64_t n_groups, int n_comp, int is_complex, void* stream),
+                ((T*)out, (const T*)x, (T)tau, n_groups, n_comp, is_complex, (cudaStream_t)stream))
+
+// ------------------------------------------------------------------------------------------------ reductions
+constexpr int RD_BLOCK = 256;
+constexpr int RD_CTAS_PER_SM = 4;
+
+enum RdOp { RD_SUMSQ, RD_DIFFSUMSQ, RD_SUMABS, RD_DOT, RD_MIN, RD_MAX };
+
+// Workspace layout (doubles): [0 .. 4*max_blocks) partials, then one 8-byte ticket slot.
+extern "C" int64_t pcs_reduce_workspace_bytes(void) {
+    return (int64_t)(4 * (int64_t)pcs::num_sms() * 8 + 16) * 8;
+}
+
+template <typename T, int OP>
+__global__ void __launch_bounds__(RD_BLOCK) reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, int64_t n,
+                                                          double* __restrict__ out, double* partials,
+                                                          unsigned int* ticket) {
+    __shared__ double sm[RD_BLOCK / 32];
+    const int64_t stride = (int64_t)gridDim.x * RD_BLOCK;
+    double acc[1] = {0.0};
+    for (int64_t i = (int64_t)blockIdx.x * RD_BLOCK + threadIdx.x; i < n; i += stride) {
+        double a = (double)x[i];
+        if (OP == RD_SUMSQ) acc[0] += a * a;
+        if (OP == RD_DIFFSUMSQ) { double d = a - (double)y[i]; acc[0] += d * d; }
+        if (OP == RD_SUMABS) acc[0] += fabs(a);
+        if (OP == RD_DOT) acc[0] += a * (double)y[i];
+    }
+    grid_sum_finish<1, RD_BLOCK>(acc, partials, ticket, out, sm);
+}
+
+template <typename T, int OP>
+static int reduce_launch(const T* x, const T* y, int64_t n, double* out, void* ws, cudaStream_t s, const char* what) {
+    PCS_REQUIRE(n >= 0 && out && ws, "%s: bad arguments", what);
+    PCS_REQUIRE(n == 0 || (x && (OP != RD_DIFFSUMSQ && OP != RD_DOT || y)), "%s: null pointer", what);
+    int grid = grid_for(n, RD_BLOCK, RD_CTAS_PER_SM);
+    double* partials = (double*)ws;
+    unsigned int* ticket = (unsigned int*)(partials + 4 * (int64_t)pcs::num_sms() * 8);
+    reduce_kernel<T, OP><<<grid, RD_BLOCK, 0, s>>>(x, y, n, out, partials, ticket);
+    return check_launch(what);
+}
+
+#define PCS_REDUCE1(name, OP)                                                                                  \
+    template <typename T> static int name##_impl(const T* x, int64_t n, double* out, void* ws, cudaStream_t s) { \
+        return reduce_launch<T, OP>(x, nullptr, n, out, ws, s, #name);                                         \
+    }                                                                                                          \
+    PCS_EXPORT_REAL(name, (const void* x, int64_t n, void* out_f64, void* workspace, void* stream),             \
+                    ((const T*)x, n, (double*)out_f64, workspace, (cudaStream_t)stream))
+#define PCS_REDUCE2(name, OP)                                                                                  \
+    template <typename T>                                                                                      \
+    static int name##_impl(const T* x, const T* y, int64_t n, double* out, void* ws, cudaStream_t s) {         \
+        return reduce_launch<T, OP>(x, y, n, out, ws, s, #name);                                               \
+    }                                                                                                          \
+    PCS_EXPORT_REAL(name, (const void* x, const void* y, int64_t n, void* out_f64, void* workspace, void* stream), \
+                    ((const T*)x, (const T*)y, n, (double*)out_f64, workspace, (cudaStream_t)stream))
+
+PCS_REDUCE1(pcs_reduce_sumsq, RD_SUMSQ)          // ||x||^2           (np.linalg.norm, opt/proxalgs.py:372-383)
+PCS_REDUCE1(pcs_reduce_sumabs, RD_SUMABS)        // sum |x|           (L1Norm.__call__, func/penalty.py:240-241)
+PCS_REDUCE2(pcs_reduce_diffsumsq, RD_DIFFSUMSQ)  // ||x - y||^2
+PCS_REDUCE2(pcs_reduce_dot, RD_DOT)              // <x, y>
+
+// min and max in one pass (IndicatorFunctional.__call__ conditions, func/penalty.py:610,666)
+template <typename T>
+__global__ void __launch_bounds__(RD_BLOCK) minmax_kernel(const T* __restrict__ x, int64_t n, double* out,
+                                                          double* partials, unsigned int* ticket) {
+    __shared__ double smn[RD_BLOCK / 32], smx[RD_BLOCK / 32];
+    __shared__ bool is_last;
+    const int64_t stride = (int64_t)gridDim.x * RD_BLOCK;
+    double mn = INFINITY, mx = -INFINITY;
+    for (int64_t i = (int64_t)blockIdx.x * RD_BLOCK + threadIdx.x; i < n; i += stride) {
+        double a = (double)x[i];
+        mn = fmin(mn, a);
+        mx = fmax(mx, a);
+    }
+    auto blockminmax = [&]() {
+        for (int o = 16; o > 0; o >>= 1) {
+            mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+            mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        }
+        if ((threadIdx.x & 31) == 0) { smn[threadIdx.x >> 5] = mn; smx[threadIdx.x >> 5] = mx; }
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            mn = threadIdx.x < RD_BLOCK / 32 ? smn[threadIdx.x] : INFINITY;
+            mx = threadIdx.x < RD_BLOCK / 32 ? smx[threadIdx.x] : -INFINITY;
+            for (int o = 16; o > 0; o >>= 1) {
+                mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+                mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            }
+        }
+    };
+    blockminmax();
+    if (threadIdx.x == 0) {
+        partials[blockIdx.x] = mn;
+        partials[gridDim.x + blockIdx.x] = mx;
+        __threadfence();
+        is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        mn = INFINITY; mx = -INFINITY;
+        for (int i = threadIdx.x; i < gridDim.x; i += RD_BLOCK) {
+            mn = fmin(mn, __ldcg(&partials[i]));
+            mx = fmax(mx, __ldcg(&partials[gridDim.x + i]));
+        }
+        __syncthreads();
+        blockminmax();
+        if (threadIdx.x == 0) { out[0] = mn; out[1] = mx; *ticket = 0u; }
+    }
+}
+
+template <typename T> static int pcs_reduce_minmax_impl(const T* x, int64_t n, double* out, void* ws, cudaStream_t s) {
+    PCS_REQUIRE(n >= 0 && out && ws && (n == 0 || x), "pcs_reduce_minmax: bad arguments");
+    int grid = grid_for(n, RD_BLOCK, RD_CTAS_PER_SM);
+    double* partials = (double*)ws;
+    unsigned int* ticket = (unsigned int*)(partials + 4 * (int64_t)pcs::num_sms() * 8);
+    minmax_kernel<T><<<grid, RD_BLOCK, 0, s>>>(x, n, out, partials, ticket);
+    return check_launch("pcs_reduce_minmax");
+}
+PCS_EXPORT_REAL(pcs_reduce_minmax, (const void* x, int64_t n, void* out2_f64, void* workspace, void* stream),
+                ((const T*)x, n, (double*)out2_f64, workspace, (cudaStream_t)stream))
+
+// sum over groups of the group 2-norm, planes layout (L21Norm.__call__, func/penalty.py:548-549)
+template <typename T>
+__global__ void __launch_bounds__(RD_BLOCK) sumgroupnorm_kernel(const T* __restrict__ x, int64_t G, int C, int cplx,
+                                                                double* out, double* partials, unsigned int* ticket) {
+    __shared__ double sm[RD_BLOCK / 32];
+    const int64_t stride = (int64_t)gridDim.x * RD_BLOCK;
+    const int64_t e = cplx ? 2 : 1;
+    double acc[1] = {0.0};
+    for (int64_t g = (int64_t)blockIdx.x * RD_BLOCK + threadIdx.x; g < G; g += stride) {
+        double ss = 0.0;
+        for (int c = 0; c < C; ++c)
+            for (int k = 0; k < e; ++k) {
+                double v = (double)x[((int64_t)c * G + g) * e + k];
+                ss += v * v;
+            }
+        acc[0] += sqrt(ss);
+    }
+    grid_sum_finish<1, RD_BLOCK>(acc, partials, ticket, out, sm);
+}
+
+template <typename T>
+static int pcs_reduce_sumgroupnorm_impl(const T* x, int64_t G, int C, int cplx, double* out, void* ws, cudaStream_t s) {
+    PCS_REQUIRE(G >= 0 && C >= 1 && out && ws && (G == 0 || x), "pcs_reduce_sumgroupnorm: bad arguments");
+    int grid = grid_for(G, RD_BLOCK, RD_CTAS_PER_SM);
+    double* partials = (double*)ws;
+    unsigned int* ticket = (unsigned int*)(partials + 4 * (int64_t)pcs::num_sms() * 8);
+    sumgroupnorm_kernel<T><<<grid, RD_BLOCK, 0, s>>>(x, G, C, cplx, out, partials, ticket);
+    return check_launch("pcs_reduce_sumgroupnorm");
+}
+PCS_EXPORT_REAL(pcs_reduce_sumgroupnorm,
+                (const void* x, int64_t n_groups, int n_comp, int is_complex, void* out_f64, void* workspace,
+                 void* stream),
+                ((const T*)x, n_groups, n_comp, is_complex, (double*)out_f64, workspace, (cudaStream_t)stream))
+
+// out = x * f(s) where s is a device-resident double: mode 0: f = clip(1 - tau/sqrt(s), 0) (L2Norm.prox,
+// func/penalty.py:23-70 via proj_l2_ball math/prox.py:207-210 -> x - tau*proj(x/tau) = x*max(1 - tau/||x||, 0));
+// mode 1: f = (sqrt(s) <= radius ? 1 : radius/sqrt(s)) (proj_l2_ball); mode 2: f = p/sqrt(s).  s holds ||x||^2.
+template <typename T>
+__global__ void __launch_bounds__(EW_BLOCK) scale_by_norm_kernel(T* __restrict__ out, const T* __restrict__ x,
+                                                                 const double* __restrict__ s, double p, int mode,
+                                                                 int64_t n) {
+    const double nrm = sqrt(s[0]);
+    double f;
+    if (mode == 0) {
+        // reference: x - tau * proj_l2_ball(x / tau, 1): ||x/tau|| <= 1 -> x - x = 0, else x - tau*(x/tau)/||x/tau||
+        f = (nrm / p <= 1.0) ? 0.0 : 1.0 - p / nrm;
+    } else if (mode == 1) {
+        f = (nrm <= p) ? 1.0 : p / nrm;
+    } else {
+        f = nrm > 0.0 ? p / nrm : 0.0;   // mode 2: rescale to norm p (power iteration)
+    }
+    const T ft = (T)f;
+    const int64_t stride = (int64_t)gridDim.x * EW_BLOCK;
+    for (int64_t i = (int64_t)blockIdx.x * EW_BLOCK + threadIdx.x; i < n; i += stride) out[i] = ft * x[i];
+}
+
+template <typename T>
+static int pcs_scale_by_norm_impl(T* out, const T* x, const double* sumsq, double p, int mode, int64_t n,
+                                  cudaStream_t s) {
+    PCS_REQUIRE(n >= 0 && (n == 0 || (out && x && sumsq)) && (mode >= 0 && mode <= 2), "pcs_scale_by_norm: bad arguments");
+    if (n == 0) return PCS_OK;
+    scale_by_norm_kernel<T><<<grid_for(n, EW_BLOCK, EW_CTAS_PER_SM), EW_BLOCK, 0, s>>>(out, x, sumsq, p, mode, n);
+    return check_launch("pcs_scale_by_norm");
+}
+PCS_EXPORT_REAL(pcs_scale_by_norm,
+                (void* out, const void* x, const void* sumsq_f64, double param, int mode, int64_t n, void* stream),
+                ((T*)out, (const T*)x, (const double*)sumsq_f64, param, mode, n, (cudaStream_t)stream))

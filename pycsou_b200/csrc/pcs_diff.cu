@@ -1,0 +1,182 @@
+// libpcsb200: finite-difference stencils (FirstDerivative / SecondDerivative / Gradient / Laplacian), sm_100a.
+//
+// Replaces pylops v1.x FirstDerivative / SecondDerivative / Gradient / Laplacian reached from
+// pycsou/linop/diff.py:128-130, 218-219, 882, 957.  Boundary rules restated in
+// oracle/pylops_standin.py.  Any n-D C-order array differentiated along one axis is viewed as
+// (outer, n, inner); consecutive threads walk consecutive flat indices, so every access is coalesced and the
+// +-inner neighbours are served by L1/L2 (HBM sees each element once).
+#include "pcs_diff.cuh"
+
+using namespace pcs;
+
+constexpr int DF_BLOCK = 256;
+constexpr int DF_CTAS_PER_SM = 8;
+
+template <typename T, bool ADJ, bool SECOND>
+__global__ void __launch_bounds__(DF_BLOCK) deriv_kernel(T* __restrict__ out, const T* __restrict__ x, int64_t outer,
+                                                         int64_t n, int64_t inner, int kind, int edge, T inv_h,
+                                                         int accumulate) {
+    const int64_t total = outer * n * inner;
+    const int64_t stride = (int64_t)gridDim.x * DF_BLOCK;
+    for (int64_t f = (int64_t)blockIdx.x * DF_BLOCK + threadIdx.x; f < total; f += stride) {
+        const int64_t i = (f / inner) % n;
+        T v;
+        if (SECOND) v = ADJ ? d2_adj<T>(x + f, i, n, inner, edge, inv_h) : d2_fwd<T>(x + f, i, n, inner, edge, inv_h);
+        else v = ADJ ? d1_adj<T>(x + f, i, n, inner, kind, edge, inv_h) : d1_fwd<T>(x + f, i, n, inner, kind, edge, inv_h);
+        out[f] = accumulate ? out[f] + v : v;
+    }
+}
+
+template <typename T, bool ADJ, bool SECOND>
+static int deriv_launch(T* out, const T* x, int64_t outer, int64_t n, int64_t inner, int kind, int edge, double step,
+                        int accumulate, cudaStream_t s, const char* what) {
+    PCS_REQUIRE(outer >= 0 && n >= 0 && inner >= 0, "%s: negative dimension", what);
+    PCS_REQUIRE(kind >= 0 && kind <= 2, "%s: kind must be 0 (forward), 1 (centered) or 2 (backward)", what);
+    PCS_REQUIRE(step != 0.0, "%s: zero step", what);
+    const int64_t total = outer * n * inner;
+    if (total == 0) return PCS_OK;
+    PCS_REQUIRE(out && x, "%s: null pointer", what);
+    PCS_REQUIRE(out != x, "%s: in-place stencils are not allowed (caller ping-pongs)", what);
+    PCS_REQUIRE(!SECOND || !edge || n >= 3, "%s: edge=True needs at least 3 samples along the axis", what);
+    PCS_REQUIRE(SECOND || kind != 1 || !edge || n >= 2, "%s: edge=True needs at least 2 samples along the axis", what);
+    const T inv_h = SECOND ? (T)(1.0 / (step * step)) : (T)(1.0 / step);
+    deriv_kernel<T, ADJ, SECOND><<<grid_for(total, DF_BLOCK, DF_CTAS_PER_SM), DF_BLOCK, 0, s>>>(
+        out, x, outer, n, inner, kind, edge, inv_h, accumulate);
+    return check_launch(what);
+}
+
+#define DERIV_PARAMS                                                                                               \
+    (void* out, const void* x, int64_t outer, int64_t n, int64_t inner, int kind, int edge, double step,           \
+     int accumulate, void* stream)
+#define DERIV_ARGS ((T*)out, (const T*)x, outer, n, inner, kind, edge, step, accumulate, (cudaStream_t)stream)
+
+template <typename T>
+static int pcs_firstderiv_fwd_impl(T* o, const T* x, int64_t a, int64_t n, int64_t b, int k, int e, double h, int acc,
+                                   cudaStream_t s) {
+    return deriv_launch<T, false, false>(o, x, a, n, b, k, e, h, acc, s, "pcs_firstderiv_fwd");
+}
+PCS_EXPORT_REAL(pcs_firstderiv_fwd, DERIV_PARAMS, DERIV_ARGS)
+template <typename T>
+static int pcs_firstderiv_adj_impl(T* o, const T* x, int64_t a, int64_t n, int64_t b, int k, int e, double h, int acc,
+                                   cudaStream_t s) {
+    return deriv_launch<T, true, false>(o, x, a, n, b, k, e, h, acc, s, "pcs_firstderiv_adj");
+}
+PCS_EXPORT_REAL(pcs_firstderiv_adj, DERIV_PARAMS, DERIV_ARGS)
+template <typename T>
+static int pcs_secondderiv_fwd_impl(T* o, const T* x, int64_t a, int64_t n, int64_t b, int k, int e, double h, int acc,
+                                    cudaStream_t s) {
+    return deriv_launch<T, false, true>(o, x, a, n, b, 0, e, h, acc, s, "pcs_secondderiv_fwd");
+}
+PCS_EXPORT_REAL(pcs_secondderiv_fwd, DERIV_PARAMS, DERIV_ARGS)
+template <typename T>
+static int pcs_secondderiv_adj_impl(T* o, const T* x, int64_t a, int64_t n, int64_t b, int k, int e, double h, int acc,
+                                    cudaStream_t s) {
+    return deriv_launch<T, true, true>(o, x, a, n, b, 0, e, h, acc, s, "pcs_secondderiv_adj");
+}
+PCS_EXPORT_REAL(pcs_secondderiv_adj, DERIV_PARAMS, DERIV_ARGS)
+
+// ------------------------------------------------------------------------------------------------ 2-D gradient
+// out = [d/daxis0 ; d/daxis1] (two planes of H*W), pylops Gradient = VStack of per-axis FirstDerivative.
+template <typename T>
+__global__ void __launch_bounds__(DF_BLOCK) grad2d_fwd_kernel(T* __restrict__ out, const T* __restrict__ x, int64_t H,
+                                                              int64_t W, int kind, int edge, T ih0, T ih1) {
+    const int64_t N = H * W, stride = (int64_t)gridDim.x * DF_BLOCK;
+    for (int64_t f = (int64_t)blockIdx.x * DF_BLOCK + threadIdx.x; f < N; f += stride) {
+        const int64_t r = f / W, c = f - r * W;
+        out[f] = d1_fwd<T>(x + f, r, H, W, kind, edge, ih0);
+        out[N + f] = d1_fwd<T>(x + f, c, W, 1, kind, edge, ih1);
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(DF_BLOCK) grad2d_adj_kernel(T* __restrict__ out, const T* __restrict__ z, int64_t H,
+                                                              int64_t W, int kind, int edge, T ih0, T ih1) {
+    const int64_t N = H * W, stride = (int64_t)gridDim.x * DF_BLOCK;
+    for (int64_t f = (int64_t)blockIdx.x * DF_BLOCK + threadIdx.x; f < N; f += stride) {
+        const int64_t r = f / W, c = f - r * W;
+        out[f] = d1_adj<T>(z + f, r, H, W, kind, edge, ih0) + d1_adj<T>(z + N + f, c, W, 1, kind, edge, ih1);
+    }
+}
+
+template <typename T>
+static int grad2d_check(const void* out, const void* x, int64_t H, int64_t W, int kind, int edge, double s0, double s1,
+                        const char* what) {
+    PCS_REQUIRE(H >= 0 && W >= 0, "%s: negative dimension", what);
+    PCS_REQUIRE(kind >= 0 && kind <= 2, "%s: kind must be 0 (forward), 1 (centered) or 2 (backward)", what);
+    PCS_REQUIRE(s0 != 0.0 && s1 != 0.0, "%s: zero step", what);
+    if (H * W == 0) return PCS_OK;
+    PCS_REQUIRE(out && x && out != x, "%s: null or aliased pointer", what);
+    PCS_REQUIRE(kind != 1 || !edge || (H >= 2 && W >= 2), "%s: centered+edge needs >= 2 samples per axis", what);
+    return PCS_OK;
+}
+
+template <typename T>
+static int pcs_grad2d_fwd_impl(T* out, const T* x, int64_t H, int64_t W, int kind, int edge, double s0, double s1,
+                               cudaStream_t s) {
+    int rc = grad2d_check<T>(out, x, H, W, kind, edge, s0, s1, "pcs_grad2d_fwd");
+    if (rc || H * W == 0) return rc;
+    grad2d_fwd_kernel<T><<<grid_for(H * W, DF_BLOCK, DF_CTAS_PER_SM), DF_BLOCK, 0, s>>>(out, x, H, W, kind, edge,
+                                                                                      (T)(1.0 / s0), (T)(1.0 / s1));
+    return check_launch("pcs_grad2d_fwd");
+}
+PCS_EXPORT_REAL(pcs_grad2d_fwd,
+                (void* out, const void* x, int64_t H, int64_t W, int kind, int edge, double step0, double step1,
+                 void* stream),
+                ((T*)out, (const T*)x, H, W, kind, edge, step0, step1, (cudaStream_t)stream))
+
+template <typename T>
+static int pcs_grad2d_adj_impl(T* out, const T* z, int64_t H, int64_t W, int kind, int edge, double s0, double s1,
+                               cudaStream_t s) {
+    int rc = grad2d_check<T>(out, z, H, W, kind, edge, s0, s1, "pcs_grad2d_adj");
+    if (rc || H * W == 0) return rc;
+    grad2d_adj_kernel<T><<<grid_for(H * W, DF_BLOCK, DF_CTAS_PER_SM), DF_BLOCK, 0, s>>>(out, z, H, W, kind, edge,
+                                                                                      (T)(1.0 / s0), (T)(1.0 / s1));
+    return check_launch("pcs_grad2d_adj");
+}
+PCS_EXPORT_REAL(pcs_grad2d_adj,
+                (void* out, const void* z, int64_t H, int64_t W, int kind, int edge, double step0, double step1,
+                 void* stream),
+                ((T*)out, (const T*)z, H, W, kind, edge, step0, step1, (cudaStream_t)stream))
+
+// ------------------------------------------------------------------------------------------------ 2-D Laplacian
+// w0 * D2(axis0) + w1 * D2(axis1)  (pylops Laplacian; pycsou/linop/diff.py:946-957).  Not symmetric at the edges
+// when edge=True, hence a distinct adjoint stencil.
+template <typename T, bool ADJ>
+__global__ void __launch_bounds__(DF_BLOCK) lap2d_kernel(T* __restrict__ out, const T* __restrict__ x, int64_t H,
+                                                         int64_t W, int edge, T w0ih, T w1ih) {
+    const int64_t N = H * W, stride = (int64_t)gridDim.x * DF_BLOCK;
+    for (int64_t f = (int64_t)blockIdx.x * DF_BLOCK + threadIdx.x; f < N; f += stride) {
+        const int64_t r = f / W, c = f - r * W;
+        T a = ADJ ? d2_adj<T>(x + f, r, H, W, edge, T(1)) : d2_fwd<T>(x + f, r, H, W, edge, T(1));
+        T b = ADJ ? d2_adj<T>(x + f, c, W, 1, edge, T(1)) : d2_fwd<T>(x + f, c, W, 1, edge, T(1));
+        out[f] = w0ih * a + w1ih * b;
+    }
+}
+
+template <typename T, bool ADJ>
+static int lap2d_launch(T* out, const T* x, int64_t H, int64_t W, double w0, double w1, double s0, double s1, int edge,
+                        cudaStream_t s, const char* what) {
+    PCS_REQUIRE(H >= 0 && W >= 0 && s0 != 0.0 && s1 != 0.0, "%s: bad dimensions or zero step", what);
+    if (H * W == 0) return PCS_OK;
+    PCS_REQUIRE(out && x && out != x, "%s: null or aliased pointer", what);
+    PCS_REQUIRE(!edge || (H >= 3 && W >= 3), "%s: edge=True needs >= 3 samples per axis", what);
+    lap2d_kernel<T, ADJ><<<grid_for(H * W, DF_BLOCK, DF_CTAS_PER_SM), DF_BLOCK, 0, s>>>(
+        out, x, H, W, edge, (T)(w0 / (s0 * s0)), (T)(w1 / (s1 * s1)));
+    return check_launch(what);
+}
+#define LAP_PARAMS                                                                                              \
+    (void* out, const void* x, int64_t H, int64_t W, double w0, double w1, double step0, double step1, int edge, \
+     void* stream)
+#define LAP_ARGS ((T*)out, (const T*)x, H, W, w0, w1, step0, step1, edge, (cudaStream_t)stream)
+template <typename T>
+static int pcs_laplacian2d_fwd_impl(T* o, const T* x, int64_t H, int64_t W, double w0, double w1, double s0, double s1,
+                                    int e, cudaStream_t s) {
+    return lap2d_launch<T, false>(o, x, H, W, w0, w1, s0, s1, e, s, "pcs_laplacian2d_fwd");
+}
+PCS_EXPORT_REAL(pcs_laplacian2d_fwd, LAP_PARAMS, LAP_ARGS)
+template <typename T>
+static int pcs_laplacian2d_adj_impl(T* o, const T* x, int64_t H, int64_t W, double w0, double w1, double s0, double s1,
+                                    int e, cudaStream_t s) {
+    return lap2d_launch<T, true>(o, x, H, W, w0, w1, s0, s1, e, s, "pcs_laplacian2d_adj");
+}
+PCS_EXPORT_REAL(pcs_laplacian2d_adj, LAP_PARAMS, LAP_ARGS)

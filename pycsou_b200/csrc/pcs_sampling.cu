@@ -1,0 +1,171 @@
+// libpcsb200: gather / scatter kernels behind Masking, DownSampling and SubSampling (sm_100a).
+//
+// Replaces numpy boolean fancy indexing in pycsou/linop/sampling.py:190-196 (Masking / DownSampling) and
+// pylops.Restriction (pycsou/linop/sampling.py:121) -- SURVEY.md rows a15-a17.  Masks are turned into a sorted
+// int64 index list once at construction; the kernels move opaque 4/8/16-byte elements, so they serve
+// float32, float64/complex64 and complex128 alike and are bit-exact by construction.
+//
+// (outer, n, inner) view for Restriction along an axis: out[o, j, k] = x[o, idx[j], k].
+#include "pcs_common.cuh"
+
+using namespace pcs;
+
+constexpr int SG_BLOCK = 256;
+
+template <typename E>
+__global__ void __launch_bounds__(SG_BLOCK) take_kernel(E* __restrict__ out, const E* __restrict__ x,
+                                                        const int64_t* __restrict__ idx, int64_t outer, int64_t n,
+                                                        int64_t m, int64_t inner) {
+    const int64_t total = outer * m * inner, stride = (int64_t)gridDim.x * SG_BLOCK;
+    for (int64_t f = (int64_t)blockIdx.x * SG_BLOCK + threadIdx.x; f < total; f += stride) {
+        const int64_t k = f % inner, j = (f / inner) % m, o = f / (inner * m);
+        out[f] = x[(o * n + idx[j]) * inner + k];
+    }
+}
+
+// out must be zero-filled by the caller (the C wrapper does it); duplicates: last writer wins is NOT guaranteed on a
+// GPU, so the host wrapper rejects duplicate indices for the adjoint (pylops assignment semantics need an order).
+template <typename E>
+__global__ void __launch_bounds__(SG_BLOCK) put_kernel(E* __restrict__ out, const E* __restrict__ y,
+                                                       const int64_t* __restrict__ idx, int64_t outer, int64_t n,
+                                                       int64_t m, int64_t inner) {
+    const int64_t total = outer * m * inner, stride = (int64_t)gridDim.x * SG_BLOCK;
+    for (int64_t f = (int64_t)blockIdx.x * SG_BLOCK + threadIdx.x; f < total; f += stride) {
+        const int64_t k = f % inner, j = (f / inner) % m, o = f / (inner * m);
+        out[(o * n + idx[j]) * inner + k] = y[f];
+    }
+}
+
+template <typename E>
+static int take_launch(void* out, const void* x, const int64_t* idx, int64_t outer, int64_t n, int64_t m,
+                       int64_t inner, cudaStream_t s) {
+    const int64_t total = outer * m * inner;
+    if (total == 0) return PCS_OK;
+    take_kernel<E><<<grid_for(total, SG_BLOCK, 8), SG_BLOCK, 0, s>>>((E*)out, (const E*)x, idx, outer, n, m, inner);
+    return check_launch("pcs_take");
+}
+
+template <typename E>
+static int put_launch(void* out, const void* y, const int64_t* idx, int64_t outer, int64_t n, int64_t m, int64_t inner,
+                      cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(out, 0, (size_t)(outer * n * inner) * sizeof(E), s);
+    if (e != cudaSuccess) {
+        set_error("pcs_put: memset failed: %s", cudaGetErrorString(e));
+        return PCS_ERR_CUDA;
+    }
+    const int64_t total = outer * m * inner;
+    if (total == 0) return PCS_OK;
+    put_kernel<E><<<grid_for(total, SG_BLOCK, 8), SG_BLOCK, 0, s>>>((E*)out, (const E*)y, idx, outer, n, m, inner);
+    return check_launch("pcs_put");
+}
+
+struct alignas(16) B16 { uint64_t a, b; };
+
+// out[(o, j, k)] = x[(o, idx[j], k)], element size in bytes in {4, 8, 16}
+extern "C" int pcs_take(void* out, const void* x, const void* idx_i64, int64_t outer, int64_t n, int64_t m,
+                        int64_t inner, int elem_bytes, void* stream) {
+    PCS_REQUIRE(outer >= 0 && n >= 0 && m >= 0 && inner >= 0, "pcs_take: negative dimension");
+    PCS_REQUIRE(outer * m * inner == 0 || (out && x && idx_i64), "pcs_take: null pointer");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t* idx = (const int64_t*)idx_i64;
+    switch (elem_bytes) {
+        case 4: return take_launch<uint32_t>(out, x, idx, outer, n, m, inner, s);
+        case 8: return take_launch<uint64_t>(out, x, idx, outer, n, m, inner, s);
+        case 16: return take_launch<B16>(out, x, idx, outer, n, m, inner, s);
+    }
+    set_error("pcs_take: element size must be 4, 8 or 16 bytes (got %d)", elem_bytes);
+    return PCS_ERR_ARG;
+}
+
+// out = zeros(outer, n, inner); out[(o, idx[j], k)] = y[(o, j, k)]  (indices must be unique)
+extern "C" int pcs_put(void* out, const void* y, const void* idx_i64, int64_t outer, int64_t n, int64_t m,
+                       int64_t inner, int elem_bytes, void* stream) {
+    PCS_REQUIRE(outer >= 0 && n >= 0 && m >= 0 && inner >= 0, "pcs_put: negative dimension");
+    PCS_REQUIRE(outer * n * inner == 0 || out, "pcs_put: null output");
+    PCS_REQUIRE(outer * m * inner == 0 || (y && idx_i64), "pcs_put: null pointer");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t* idx = (const int64_t*)idx_i64;
+    if (outer * n * inner == 0) return PCS_OK;
+    switch (elem_bytes) {
+        case 4: return put_launch<uint32_t>(out, y, idx, outer, n, m, inner, s);
+        case 8: return put_launch<uint64_t>(out, y, idx, outer, n, m, inner, s);
+        case 16: return put_launch<B16>(out, y, idx, outer, n, m, inner, s);
+    }
+    set_error("pcs_put: element size must be 4, 8 or 16 bytes (got %d)", elem_bytes);
+    return PCS_ERR_ARG;
+}
+
+// Boolean mask -> number of set entries and their sorted positions.  Single-block-per-chunk two-pass compaction:
+// pass 1 counts per chunk, host-free exclusive scan by one block, pass 2 writes indices.  Construction-time only.
+constexpr int MK_CHUNK = 4096;
+
+__global__ void mask_count_kernel(const uint8_t* __restrict__ mask, int64_t n, int64_t* __restrict__ counts) {
+    __shared__ int sm[SG_BLOCK / 32];
+    const int64_t base = (int64_t)blockIdx.x * MK_CHUNK;
+    int c = 0;
+    for (int e = threadIdx.x; e < MK_CHUNK; e += SG_BLOCK) {
+        const int64_t i = base + e;
+        if (i < n && mask[i]) ++c;
+    }
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int w = 0; w < SG_BLOCK / 32; ++w) t += sm[w];
+        counts[blockIdx.x] = t;
+    }
+}
+
+__global__ void mask_scan_kernel(int64_t* counts, int64_t nchunks, int64_t* total) {
+    // one thread: nchunks = n / 4096 is small (<= 262144 for a 2^30 mask); construction-time only
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        int64_t run = 0;
+        for (int64_t i = 0; i < nchunks; ++i) {
+            int64_t c = counts[i];
+            counts[i] = run;
+            run += c;
+        }
+        *total = run;
+    }
+}
+
+__global__ void mask_write_kernel(const uint8_t* __restrict__ mask, int64_t n, const int64_t* __restrict__ offsets,
+                                  int64_t* __restrict__ idx) {
+    // one warp per chunk keeps the output sorted: ballot + popc prefix
+    const int lane = threadIdx.x & 31;
+    const int64_t chunk = (int64_t)blockIdx.x * (SG_BLOCK / 32) + (threadIdx.x >> 5);
+    const int64_t base = chunk * MK_CHUNK;
+    if (base >= n) return;
+    int64_t pos = offsets[chunk];
+    for (int e = 0; e < MK_CHUNK; e += 32) {
+        const int64_t i = base + e + lane;
+        const bool set = (i < n) && mask[i];
+        const unsigned b = __ballot_sync(0xffffffffu, set);
+        if (set) idx[pos + __popc(b & ((1u << lane) - 1u))] = i;
+        pos += __popc(b);
+    }
+}
+
+extern "C" int64_t pcs_mask_workspace_bytes(int64_t n) { return ((n + MK_CHUNK - 1) / MK_CHUNK + 2) * 8; }
+
+// Phase 1: count.  total_out (device int64) receives popcount(mask); workspace keeps the chunk offsets for phase 2.
+extern "C" int pcs_mask_count(const void* mask_u8, int64_t n, void* workspace, void* total_out_i64, void* stream) {
+    PCS_REQUIRE(n >= 0 && workspace && total_out_i64 && (n == 0 || mask_u8), "pcs_mask_count: bad arguments");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t nchunks = (n + MK_CHUNK - 1) / MK_CHUNK;
+    if (nchunks > 0) mask_count_kernel<<<(unsigned)nchunks, SG_BLOCK, 0, s>>>((const uint8_t*)mask_u8, n, (int64_t*)workspace);
+    mask_scan_kernel<<<1, 32, 0, s>>>((int64_t*)workspace, nchunks, (int64_t*)total_out_i64);
+    return check_launch("pcs_mask_count");
+}
+
+// Phase 2: write the sorted positions (idx_out must hold popcount(mask) int64).
+extern "C" int pcs_mask_indices(const void* mask_u8, int64_t n, const void* workspace, void* idx_out_i64, void* stream) {
+    PCS_REQUIRE(n >= 0 && workspace && (n == 0 || (mask_u8 && idx_out_i64)), "pcs_mask_indices: bad arguments");
+    const int64_t nchunks = (n + MK_CHUNK - 1) / MK_CHUNK;
+    if (nchunks == 0) return PCS_OK;
+    const int warps = SG_BLOCK / 32;
+    mask_write_kernel<<<(unsigned)((nchunks + warps - 1) / warps), SG_BLOCK, 0, (cudaStream_t)stream>>>(
+        (const uint8_t*)mask_u8, n, (const int64_t*)workspace, (int64_t*)idx_out_i64);
+    return check_launch("pcs_mask_indices");
+}

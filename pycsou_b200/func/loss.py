@@ -1,0 +1,68 @@
+r"""Loss functionals (mirror of the hot-path part of ``pycsou/func/loss.py``).
+
+``ProximableLoss(f, data) = f(. - data)`` is ``ProxFuncPreComp(f, scale=1, shift=-data)`` (reference ``loss.py:69``);
+``DifferentiableLoss(f, data) = f.shifter(-data)`` (``loss.py:120``).  ``data`` may be a numpy array or a tensor; it is
+uploaded once, lazily, in the dtype of the first argument it meets.
+"""
+from __future__ import annotations
+
+from numbers import Number
+
+import numpy as np
+import torch
+
+from ..core.functional import DifferentiableFunctional, ProxFuncPreComp, ProximableFunctional
+from .base import IndicatorFunctional
+from .penalty import L1Norm, L2Ball, L2Norm, LInftyBall, SquaredL2Norm
+
+__all__ = ['ProximableLoss', 'DifferentiableLoss', 'L2Loss', 'SquaredL2Loss', 'L2BallLoss', 'L1Loss', 'SquaredL1Loss',
+           'L1BallLoss', 'LInftyLoss', 'LInftyBallLoss', 'ConsistencyLoss', 'KLDivergence']
+
+
+def _neg(data):
+    if isinstance(data, torch.Tensor):
+        return -data
+    return -np.asarray(data) if not isinstance(data, Number) else -data
+
+
+def ProximableLoss(func: ProximableFunctional, data) -> ProximableFunctional:
+    return ProxFuncPreComp(func, scale=1, shift=_neg(data))
+
+
+def DifferentiableLoss(func: DifferentiableFunctional, data) -> DifferentiableFunctional:
+    return func.shifter(shift=_neg(data))
+
+
+def L2Loss(dim: int, data) -> ProximableFunctional:
+    return ProximableLoss(L2Norm(dim=dim), data=data)
+
+
+def SquaredL2Loss(dim: int, data) -> DifferentiableFunctional:
+    r""":math:`\|y - x\|_2^2` (reference ``func/loss.py:165-219``)."""
+    return DifferentiableLoss(SquaredL2Norm(dim=dim), data=data)
+
+
+def L2BallLoss(dim: int, data, radius: Number = 1) -> ProximableFunctional:
+    return ProximableLoss(L2Ball(dim=dim, radius=radius), data=data)
+
+
+def L1Loss(dim: int, data) -> ProximableFunctional:
+    return ProximableLoss(L1Norm(dim=dim), data=data)
+
+
+def LInftyBallLoss(dim: int, data, radius: Number = 1) -> ProximableFunctional:
+    return ProximableLoss(LInftyBall(dim=dim, radius=radius), data=data)
+
+
+def _out_of_scope(name):
+    def ctor(*args, **kwargs):
+        raise NotImplementedError(f'{name} is outside the B200 hot path (SURVEY.md section 2 / 8(f) rank 2)')
+    ctor.__name__ = name
+    return ctor
+
+
+SquaredL1Loss = _out_of_scope('SquaredL1Loss')
+L1BallLoss = _out_of_scope('L1BallLoss')
+LInftyLoss = _out_of_scope('LInftyLoss')
+ConsistencyLoss = _out_of_scope('ConsistencyLoss')
+KLDivergence = _out_of_scope('KLDivergence')

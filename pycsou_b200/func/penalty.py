@@ -1,0 +1,181 @@
+r"""Penalty functionals on the device (mirror of the hot-path part of ``pycsou/func/penalty.py``).
+
+In scope: ``L2Norm, SquaredL2Norm, L2Ball, L1Norm, LInftyBall, L21Norm, NonNegativeOrthant,
+Segment``.  The remaining reference penalties (sort / root-find / Lambert-W proxes) raise ``NotImplementedError``.
+"""
+from __future__ import annotations
+
+from numbers import Number
+from typing import Optional, Union
+
+import numpy as np
+import torch
+
+from .. import _kernels as K
+from ..core.functional import DifferentiableFunctional, ProximableFunctional
+from ..math.prox import proj_l2_ball, proj_linfty_ball, proj_nonnegative_orthant, proj_segment, soft
+from .base import IndicatorFunctional, LpNorm
+
+__all__ = ['L2Norm', 'SquaredL2Norm', 'L2Ball', 'L1Norm', 'SquaredL1Norm', 'L1Ball', 'LInftyNorm', 'LInftyBall',
+           'L21Norm', 'NonNegativeOrthant', 'Segment', 'RealLine', 'ImagLine', 'LogBarrier', 'ShannonEntropy',
+           'QuadraticForm']
+
+
+class L2Norm(LpNorm):
+    r""":math:`\|x\|_2` (reference ``func/penalty.py:23-70``)."""
+
+    def __init__(self, dim: int):
+        super(L2Norm, self).__init__(dim=dim, proj_lq_ball=proj_l2_ball)
+
+    def _apply(self, x):
+        return float(torch.sqrt(K.sumsq(x)).item())
+
+    def _prox(self, x, tau):
+        # x - tau * proj_l2_ball(x / tau, 1)  ==  x * max(1 - tau/||x||, 0)   (one reduction + one scaling pass)
+        return K.scale_by_norm(torch.empty_like(x), x, K.sumsq(x), tau, 0)
+
+
+class SquaredL2Norm(DifferentiableFunctional):
+    r""":math:`\|x\|_2^2`, gradient :math:`2x` (reference ``func/penalty.py:73-131``)."""
+
+    def __init__(self, dim: int):
+        super(SquaredL2Norm, self).__init__(dim=dim, data=None, is_linear=False, lipschitz_cst=np.inf,
+                                            diff_lipschitz_cst=2)
+
+    def _apply(self, x):
+        return float(K.sumsq(x).item())
+
+    def _jacobianT(self, x):
+        return K.scale(torch.empty_like(x), 2.0, x)
+
+
+def L2Ball(dim: int, radius: Number) -> IndicatorFunctional:
+    """Indicator of the l2 ball (reference ``func/penalty.py:134-191``)."""
+    return IndicatorFunctional(dim=dim, condition_func=lambda x: float(torch.sqrt(K.sumsq(x)).item()) <= radius,
+                               projection_func=lambda x: proj_l2_ball.device(x, radius=radius),
+                               kind='l2ball', params=(radius,))
+
+
+class L1Norm(LpNorm):
+    r""":math:`\|x\|_1`; prox = ``x - tau*clip(x/tau, -1, 1)`` (reference ``func/penalty.py:194-245``)."""
+
+    def __init__(self, dim: int):
+        super(L1Norm, self).__init__(dim=dim, proj_lq_ball=proj_linfty_ball)
+
+    def _apply(self, x):
+        return float(K.sumabs(x).item())
+
+    def _prox(self, x, tau):
+        return K.prox_l1(torch.empty_like(x), x, tau)
+
+    def soft(self, x, tau: Number):
+        return soft(x=x, tau=tau)
+
+
+def LInftyBall(dim: int, radius: Number) -> IndicatorFunctional:
+    """Indicator of the l-infinity ball (reference ``func/penalty.py:420-477``)."""
+    def cond(x):
+        mn, mx = K.minmax(x).tolist()
+        return max(abs(mn), abs(mx)) <= radius
+    return IndicatorFunctional(dim=dim, condition_func=cond,
+                               projection_func=lambda x: proj_linfty_ball.device(x, radius=radius),
+                               kind='segment', params=(-radius, radius))
+
+
+class L21Norm(ProximableFunctional):
+    r"""Mixed :math:`\ell_{2,1}` norm :math:`\sum_g \|x_g\|_2` (reference ``func/penalty.py:480-560``).
+
+    ``groups`` is a label array of length ``dim``.  As in the reference, ``__new__`` degenerates to ``L1Norm`` when
+    all labels are distinct (or ``groups`` is None) and to ``L2Norm`` when there is a single group
+    (``penalty.py:525-530``).  The device kernels implement the *planes* layout ``groups == tile(arange(G), C)``
+    (component ``c`` of group ``g`` at ``x[c*G + g]``) -- the layout of a stacked ``Gradient`` output, i.e. isotropic
+    TV.  Arbitrary label arrays are re-ordered into that layout through a gather/scatter permutation when all groups
+    have the same size; ragged groups raise ``NotImplementedError``.
+    """
+
+    def __new__(cls, dim: int, groups=None):
+        if groups is None:
+            return L1Norm(dim=dim)
+        g = _labels(groups)
+        n_unique = np.unique(g).size
+        if n_unique == dim:
+            return L1Norm(dim=dim)
+        if n_unique == 1:
+            return L2Norm(dim=dim)
+        return super(L21Norm, cls).__new__(cls)
+
+    def __init__(self, dim: int, groups):
+        self.groups = groups
+        g = _labels(groups)
+        if g.size != dim:
+            raise ValueError('groups must have one label per coordinate.')
+        self.groups_idxs, inv, counts = np.unique(g, return_inverse=True, return_counts=True)
+        self.n_groups = int(self.groups_idxs.size)
+        if np.any(counts != counts[0]):
+            raise NotImplementedError('L21Norm with ragged groups is not supported by the device kernels')
+        self.n_comp = int(counts[0])
+        if self.n_comp > 4:
+            raise NotImplementedError('L21Norm supports at most 4 components per group')
+        planes = np.tile(np.arange(self.n_groups), self.n_comp)
+        self._is_planes = bool(np.array_equal(inv, planes))
+        if not self._is_planes:
+            # stable order of members inside each group -> position in the planes layout
+            order = np.argsort(inv, kind='stable').reshape(self.n_groups, self.n_comp)
+            self._perm_host = order.T.reshape(-1).astype(np.int64)      # planes[k] = x[perm[k]]
+        self._perm = None
+        super(L21Norm, self).__init__(dim=dim, data=None, is_differentiable=False, is_linear=False)
+
+    def _to_planes(self, x):
+        if self._is_planes:
+            return x
+        if self._perm is None or self._perm.device != x.device:
+            self._perm = torch.from_numpy(self._perm_host).to(x.device)
+        return K.take(torch.empty_like(x), x, self._perm, 1, x.numel(), 1)
+
+    def _apply(self, x):
+        return float(K.sumgroupnorm(self._to_planes(x), self.n_groups, self.n_comp).item())
+
+    def _prox(self, x, tau):
+        p = K.prox_l21(torch.empty_like(x), self._to_planes(x), tau, self.n_groups, self.n_comp)
+        if self._is_planes:
+            return p
+        return K.put(torch.empty_like(x), p, self._perm, 1, x.numel(), 1)
+
+
+def _labels(groups):
+    if isinstance(groups, torch.Tensor):
+        groups = groups.detach().cpu().numpy()
+    return np.asarray(groups).reshape(-1)
+
+
+def NonNegativeOrthant(dim: int) -> IndicatorFunctional:
+    """Indicator of the non-negative orthant (reference ``func/penalty.py:563-612``)."""
+    return IndicatorFunctional(dim=dim, condition_func=lambda x: float(K.minmax(x)[0].item()) >= 0,
+                               projection_func=lambda x: proj_nonnegative_orthant.device(x), kind='nonneg')
+
+
+def Segment(dim: int, a: Number = 0, b: Number = 1):
+    """Indicator of the box ``[a, b]^dim`` (reference ``func/penalty.py:615-668``)."""
+    def cond(x):
+        mn, mx = K.minmax(x).tolist()
+        return mn >= a and mx <= b
+    return IndicatorFunctional(dim=dim, condition_func=cond,
+                               projection_func=lambda x: proj_segment.device(x, a=a, b=b), kind='segment',
+                               params=(a, b))
+
+
+def _out_of_scope(name):
+    def ctor(*args, **kwargs):
+        raise NotImplementedError(f'{name} is outside the B200 hot path (SURVEY.md section 2 / 8(f) rank 2)')
+    ctor.__name__ = name
+    return ctor
+
+
+SquaredL1Norm = _out_of_scope('SquaredL1Norm')
+L1Ball = _out_of_scope('L1Ball')
+LInftyNorm = _out_of_scope('LInftyNorm')
+RealLine = _out_of_scope('RealLine')
+ImagLine = _out_of_scope('ImagLine')
+LogBarrier = _out_of_scope('LogBarrier')
+ShannonEntropy = _out_of_scope('ShannonEntropy')
+QuadraticForm = _out_of_scope('QuadraticForm')

@@ -1,0 +1,4 @@
+from .base import *
+from .conv import *
+from .diff import *
+from .sampling import *

@@ -1,0 +1,177 @@
+r"""Finite-difference operators (mirror of the hot-path part of ``pycsou/linop/diff.py``).
+
+``FirstDerivative`` (default ``kind='forward'``, ``edge=True``; reference ``diff.py:24-130``), ``SecondDerivative``
+(``diff.py:133-219``), ``Gradient`` (default ``kind='centered'``, ``edge=True``; ``diff.py:777-882``) and ``Laplacian``
+(``diff.py:885-957``) keep the reference's signatures and defaults.  Where the reference wraps a pylops operator,
+these factories return device-resident ``LinearOperator`` subclasses whose ``_apply`` / ``_adjoint`` launch the
+stencil kernels of ``csrc/pcs_diff.cu``.  Directional / generalised derivatives and ``Integration1D`` are out of
+scope and raise ``NotImplementedError``.
+"""
+from __future__ import annotations
+
+from numbers import Number
+from typing import Optional, Tuple, Union
+
+import numpy as np
+import torch
+
+from .. import _kernels as K
+from ..core.linop import LinearOperator
+
+__all__ = ['FirstDerivative', 'SecondDerivative', 'Gradient', 'Laplacian', 'GeneralisedDerivative',
+           'FirstDirectionalDerivative', 'SecondDirectionalDerivative', 'DirectionalGradient', 'DirectionalLaplacian',
+           'GeneralisedLaplacian', 'Integration1D']
+
+_KINDS = ('forward', 'centered', 'backward')
+
+
+def _axis_view(size, shape, axis):
+    """(outer, n, inner) view of a C-order array differentiated along ``axis``."""
+    if shape is None:
+        return 1, int(size), 1
+    shape = tuple(int(s) for s in shape)
+    if int(np.prod(shape)) != size:
+        raise ValueError('product of dims must equal N!')
+    axis = axis if axis >= 0 else len(shape) + axis
+    if not 0 <= axis < len(shape):
+        raise ValueError(f'axis {axis} is out of range for shape {shape}')
+    return int(np.prod(shape[:axis], dtype=np.int64)), shape[axis], int(np.prod(shape[axis + 1:], dtype=np.int64))
+
+
+class FirstDerivativeOperator(LinearOperator):
+    """First derivative along one axis of an n-D array (device stencil; semantics of pylops v1.x FirstDerivative)."""
+
+    def __init__(self, size, shape, axis, step, edge, dtype, kind):
+        if kind not in _KINDS:
+            raise NotImplementedError('kind must be forward, centered, or backward')
+        self.outer, self.n, self.inner = _axis_view(size, shape, axis)
+        self.step, self.edge, self.kind = float(step), bool(edge), kind
+        self.array_shape = None if shape is None else tuple(shape)
+        self.axis = axis
+        super().__init__(shape=(size, size), dtype=np.dtype(dtype))
+
+    def _apply(self, x):
+        return K.firstderiv(torch.empty_like(x), x, self.outer, self.n, self.inner, self.kind, self.edge, self.step)
+
+    def _adjoint(self, y):
+        return K.firstderiv(torch.empty_like(y), y, self.outer, self.n, self.inner, self.kind, self.edge, self.step,
+                            adjoint=True)
+
+
+class SecondDerivativeOperator(LinearOperator):
+    def __init__(self, size, shape, axis, step, edge, dtype):
+        self.outer, self.n, self.inner = _axis_view(size, shape, axis)
+        self.step, self.edge = float(step), bool(edge)
+        self.array_shape = None if shape is None else tuple(shape)
+        self.axis = axis
+        super().__init__(shape=(size, size), dtype=np.dtype(dtype))
+
+    def _apply(self, x):
+        return K.secondderiv(torch.empty_like(x), x, self.outer, self.n, self.inner, self.edge, self.step)
+
+    def _adjoint(self, y):
+        return K.secondderiv(torch.empty_like(y), y, self.outer, self.n, self.inner, self.edge, self.step, adjoint=True)
+
+
+class GradientOperator(LinearOperator):
+    r"""Stack of per-axis first derivatives, output laid out ``[d/daxis0 ; d/daxis1 ; ...]`` (pylops ``Gradient``)."""
+
+    def __init__(self, shape, step, edge, dtype, kind):
+        if kind not in _KINDS:
+            raise NotImplementedError('kind must be forward, centered, or backward')
+        self.array_shape = tuple(int(s) for s in shape)
+        nd = len(self.array_shape)
+        self.steps = tuple([float(step)] * nd) if isinstance(step, Number) else tuple(float(s) for s in step)
+        if len(self.steps) != nd:
+            raise ValueError('one sampling step per axis is required')
+        self.edge, self.kind = bool(edge), kind
+        self.N = int(np.prod(self.array_shape))
+        super().__init__(shape=(nd * self.N, self.N), dtype=np.dtype(dtype))
+
+    def _apply(self, x):
+        nd, N = len(self.array_shape), self.N
+        out = torch.empty(nd * N, dtype=x.dtype, device=x.device)
+        if nd == 2 and not x.is_complex():
+            H, W = self.array_shape
+            return K.grad2d(out, x, H, W, self.kind, self.edge, self.steps[0], self.steps[1])
+        for ax in range(nd):
+            o, n, i = _axis_view(N, self.array_shape, ax)
+            K.firstderiv(out[ax * N:(ax + 1) * N], x, o, n, i, self.kind, self.edge, self.steps[ax])
+        return out
+
+    def _adjoint(self, z):
+        nd, N = len(self.array_shape), self.N
+        out = torch.empty(N, dtype=z.dtype, device=z.device)
+        if nd == 2 and not z.is_complex():
+            H, W = self.array_shape
+            return K.grad2d(out, z, H, W, self.kind, self.edge, self.steps[0], self.steps[1], adjoint=True)
+        for ax in range(nd):
+            o, n, i = _axis_view(N, self.array_shape, ax)
+            K.firstderiv(out, z[ax * N:(ax + 1) * N], o, n, i, self.kind, self.edge, self.steps[ax], adjoint=True,
+                         accumulate=ax > 0)
+        return out
+
+
+class LaplacianOperator(LinearOperator):
+    r""":math:`w_0\,\partial^2_{axis0} + w_1\,\partial^2_{axis1}` on a 2-D array (pylops ``Laplacian``)."""
+
+    def __init__(self, shape, weights, step, edge, dtype):
+        self.array_shape = tuple(int(s) for s in shape)
+        if len(self.array_shape) != 2:
+            raise NotImplementedError('Laplacian is implemented for 2-D arrays (the reference differentiates axes 0 and 1)')
+        self.weights = (float(weights[0]), float(weights[1]))
+        self.steps = (float(step[0]), float(step[1]))
+        self.edge = bool(edge)
+        N = int(np.prod(self.array_shape))
+        super().__init__(shape=(N, N), dtype=np.dtype(dtype))
+
+    def _run(self, x, adjoint):
+        if x.is_complex():
+            raise NotImplementedError('complex Laplacian')
+        H, W = self.array_shape
+        return K.laplacian2d(torch.empty_like(x), x, H, W, self.weights[0], self.weights[1], self.steps[0],
+                             self.steps[1], self.edge, adjoint=adjoint)
+
+    def _apply(self, x):
+        return self._run(x, False)
+
+    def _adjoint(self, y):
+        return self._run(y, True)
+
+
+def FirstDerivative(size: int, shape: Optional[tuple] = None, axis: int = 0, step: float = 1.0, edge: bool = True,
+                    dtype: str = 'float64', kind: str = 'forward') -> LinearOperator:
+    return FirstDerivativeOperator(size, shape, axis, step, edge, dtype, kind)
+
+
+def SecondDerivative(size: int, shape: Optional[tuple] = None, axis: int = 0, step: float = 1.0, edge: bool = True,
+                     dtype: str = 'float64') -> LinearOperator:
+    return SecondDerivativeOperator(size, shape, axis, step, edge, dtype)
+
+
+def Gradient(shape: tuple, step: Union[tuple, float] = 1., edge: bool = True, dtype: str = 'float64',
+             kind: str = 'centered') -> LinearOperator:
+    return GradientOperator(shape, step, edge, dtype, kind)
+
+
+def Laplacian(shape: tuple, weights: Tuple[float] = (1, 1), step: Union[tuple, float] = 1., edge: bool = True,
+              dtype: str = 'float64') -> LinearOperator:
+    if isinstance(step, Number):
+        step = [step] * len(shape)
+    return LaplacianOperator(shape, weights, step, edge, dtype)
+
+
+def _out_of_scope(name):
+    def ctor(*args, **kwargs):
+        raise NotImplementedError(f'{name} is outside the B200 hot path (SURVEY.md section 2 / 8(f) rank 3)')
+    ctor.__name__ = name
+    return ctor
+
+
+GeneralisedDerivative = _out_of_scope('GeneralisedDerivative')
+FirstDirectionalDerivative = _out_of_scope('FirstDirectionalDerivative')
+SecondDirectionalDerivative = _out_of_scope('SecondDirectionalDerivative')
+DirectionalGradient = _out_of_scope('DirectionalGradient')
+DirectionalLaplacian = _out_of_scope('DirectionalLaplacian')
+GeneralisedLaplacian = _out_of_scope('GeneralisedLaplacian')
+Integration1D = _out_of_scope('Integration1D')
