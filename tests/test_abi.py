@@ -15,7 +15,7 @@ def header_symbols():
     txt = open(os.path.join(ROOT, 'include', 'pcsb200.h')).read()
     txt = re.sub(r'/\*.*?\*/', '', txt, flags=re.S)
     names = set()
-    for m in re.finditer(r'PCS_DECL_REAL\(\s*(\w+)\s*,', txt):
+    for m in re.finditer(r'^PCS_DECL_REAL\(\s*(pcs_\w+)\s*,', txt, flags=re.M):
         names.update({m.group(1) + '_f32', m.group(1) + '_f64'})
     for m in re.finditer(r'^\s*(?:int|int64_t|const char\*)\s+(pcs_\w+)\s*\(', txt, flags=re.M):
         names.add(m.group(1))

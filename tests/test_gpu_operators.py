@@ -1,0 +1,222 @@
+"""GPU parity: every stand-alone operator / prox kernel (through the C ABI) vs the numpy oracle.
+
+fp64: relative L2 <= 1e-13 (same formulas, different summation order for convolutions);
+fp32: <= 2e-6.  Index / mask work: bit-exact.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import np_oracle as O
+from tests.helpers import rel_l2
+
+pytestmark = pytest.mark.gpu
+
+DT = [(np.float64, 1e-13), (np.float32, 3e-6)]
+
+
+def rng(seed=0):
+    return np.random.default_rng(seed)
+
+
+@pytest.mark.parametrize('dtype,tol', DT)
+@pytest.mark.parametrize('kind', ['forward', 'centered', 'backward'])
+@pytest.mark.parametrize('edge', [True, False])
+@pytest.mark.parametrize('shape,axis', [(None, 0), ((7, 9), 0), ((7, 9), 1), ((4, 5, 6), 1), ((4, 5, 6), -1), ((2, 3), 0)])
+def test_first_derivative(dtype, tol, kind, edge, shape, axis):
+    from pycsou_b200.linop.diff import FirstDerivative
+    n = 37 if shape is None else int(np.prod(shape))
+    x, z = rng(1).standard_normal(n).astype(dtype), rng(2).standard_normal(n).astype(dtype)
+    D = FirstDerivative(n, shape=shape, axis=axis, step=0.7, edge=edge, dtype=np.dtype(dtype).name, kind=kind)
+    Do = O.FirstDerivative(n, shape=shape, axis=axis, step=0.7, edge=edge, kind=kind)
+    assert rel_l2(D(x), Do.matvec(x.astype(np.float64))) < tol
+    assert rel_l2(D.adjoint(z), Do.rmatvec(z.astype(np.float64))) < tol
+    assert isinstance(D(x), np.ndarray) and D(x).dtype == dtype
+
+
+@pytest.mark.parametrize('dtype,tol', DT)
+@pytest.mark.parametrize('edge', [True, False])
+@pytest.mark.parametrize('shape,axis', [(None, 0), ((7, 9), 0), ((7, 9), 1), ((3, 4), 1)])
+def test_second_derivative(dtype, tol, edge, shape, axis):
+    from pycsou_b200.linop.diff import SecondDerivative
+    n = 23 if shape is None else int(np.prod(shape))
+    x, z = rng(1).standard_normal(n).astype(dtype), rng(2).standard_normal(n).astype(dtype)
+    D = SecondDerivative(n, shape=shape, axis=axis, step=1.3, edge=edge, dtype=np.dtype(dtype).name)
+    Do = O.SecondDerivative(n, shape=shape, axis=axis, step=1.3, edge=edge)
+    assert rel_l2(D(x), Do.matvec(x.astype(np.float64))) < tol
+    assert rel_l2(D.adjoint(z), Do.rmatvec(z.astype(np.float64))) < tol
+
+
+@pytest.mark.parametrize('dtype,tol', DT)
+@pytest.mark.parametrize('kind', ['forward', 'centered', 'backward'])
+@pytest.mark.parametrize('shape', [(48, 64), (5, 3), (2, 2), (1, 9), (9, 1), (130, 257), (4, 5, 6)])
+def test_gradient(dtype, tol, kind, shape):
+    from pycsou_b200.linop.diff import Gradient
+    if kind == 'centered' and min(shape) < 2:
+        pytest.skip('pylops centered+edge needs 2 samples')
+    n, nd = int(np.prod(shape)), len(shape)
+    x, z = rng(1).standard_normal(n).astype(dtype), rng(2).standard_normal(nd * n).astype(dtype)
+    step = tuple(0.5 + 0.25 * i for i in range(nd))
+    G = Gradient(shape, step=step, kind=kind, dtype=np.dtype(dtype).name)
+    Go = O.Gradient(shape, step=list(step), kind=kind)
+    assert G.shape == (nd * n, n)
+    assert rel_l2(G(x), Go.matvec(x.astype(np.float64))) < tol
+    assert rel_l2(G.adjoint(z), Go.rmatvec(z.astype(np.float64))) < tol
+    # adjoint dot test on the device result itself
+    assert abs(np.dot(G(x).astype(np.float64), z) - np.dot(x, G.adjoint(z).astype(np.float64))) < 1e3 * tol * n
+
+
+@pytest.mark.parametrize('dtype,tol', DT)
+@pytest.mark.parametrize('edge', [True, False])
+def test_laplacian(dtype, tol, edge):
+    from pycsou_b200.linop.diff import Laplacian
+    shape = (19, 33)
+    x, z = rng(1).standard_normal(19 * 33).astype(dtype), rng(2).standard_normal(19 * 33).astype(dtype)
+    L = Laplacian(shape, weights=(1.5, 0.5), step=(1., 2.), edge=edge, dtype=np.dtype(dtype).name)
+    Lo = O.Laplacian(shape, weights=(1.5, 0.5), step=(1., 2.), edge=edge)
+    assert rel_l2(L(x), Lo.matvec(x.astype(np.float64))) < tol
+    assert rel_l2(L.adjoint(z), Lo.rmatvec(z.astype(np.float64))) < tol
+
+
+@pytest.mark.parametrize('dtype,tol', DT)
+@pytest.mark.parametrize('nh', [1, 4, 5, 65])
+def test_convolve1d(dtype, tol, nh):
+    from pycsou_b200.linop.conv import Convolve1D
+    n = 300
+    h = rng(3).random(nh)
+    x = rng(1).standard_normal(n).astype(dtype)
+    C, Co = Convolve1D(n, h, dtype=np.dtype(dtype).name), O.Convolve1D(n, h)
+    assert rel_l2(C(x), Co.matvec(x.astype(np.float64))) < tol
+    assert rel_l2(C.adjoint(x), Co.rmatvec(x.astype(np.float64))) < tol
+    # along an axis of a 2-D array
+    shape = (12, 25)
+    for axis in (0, 1):
+        C = Convolve1D(n, h[:min(nh, 9)], reshape_dims=shape, axis=axis, dtype=np.dtype(dtype).name)
+        Co = O.Convolve1D(n, h[:min(nh, 9)], reshape_dims=shape, axis=axis)
+        assert rel_l2(C(x), Co.matvec(x.astype(np.float64))) < 10 * tol
+        assert rel_l2(C.adjoint(x), Co.rmatvec(x.astype(np.float64))) < 10 * tol
+
+
+@pytest.mark.parametrize('dtype,tol', DT)
+@pytest.mark.parametrize('hshape,sep', [((15, 15), True), ((15, 15), False), ((3, 7), False), ((4, 6), True),
+                                        ((1, 1), True), ((25, 25), False)])
+@pytest.mark.parametrize('shape', [(48, 64), (70, 33), (5, 4)])
+def test_convolve2d(dtype, tol, hshape, sep, shape):
+    from pycsou_b200.linop.conv import Convolve2D
+    r = rng(4)
+    h = np.outer(r.random(hshape[0]), r.random(hshape[1])) if sep else r.random(hshape)
+    n = shape[0] * shape[1]
+    x = r.standard_normal(n).astype(dtype)
+    C, Co = Convolve2D(n, h, shape, dtype=np.dtype(dtype).name), O.Convolve2D(n, h, shape)
+    assert C.is_separable == (sep or h.size == 1 or min(hshape) == 1)
+    assert rel_l2(C(x), Co.matvec(x.astype(np.float64))) < 20 * tol
+    assert rel_l2(C.adjoint(x), Co.rmatvec(x.astype(np.float64))) < 20 * tol
+
+
+def test_sampling_bit_exact():
+    from pycsou_b200.linop.sampling import DownSampling, Masking, SubSampling
+    r = rng(5)
+    for dtype in (np.float32, np.float64, np.complex64, np.complex128):
+        n = 5000
+        x = (r.standard_normal(n) + (1j * r.standard_normal(n) if np.dtype(dtype).kind == 'c' else 0)).astype(dtype)
+        mask = r.random(n) < 0.3
+        M, Mo = Masking(n, mask, dtype=dtype), O.Masking(n, mask, dtype=dtype)
+        y = M(x)
+        assert y.dtype == dtype and np.array_equal(y, Mo.matvec(x))
+        assert np.array_equal(M.adjoint(y), Mo.rmatvec(y))
+        assert M.nb_of_samples == Mo.nb_of_samples and M.shape == Mo.shape
+    x = r.standard_normal(20 * 30)
+    for kw in (dict(downsampling_factor=3), dict(downsampling_factor=(2, 3), shape=(20, 30)),
+               dict(downsampling_factor=4, shape=(20, 30), axis=-1), dict(downsampling_factor=4, shape=(20, 30), axis=0)):
+        D, Do = DownSampling(600, **kw), O.DownSampling(600, **kw)
+        assert np.array_equal(D.downsampling_mask, Do.sampling_bool)
+        assert np.array_equal(D(x), Do.matvec(x)) and np.array_equal(D.adjoint(D(x)), Do.rmatvec(Do.matvec(x)))
+    idx = np.array([5, 0, 17, 5, 3, 17])          # duplicates: the last occurrence wins in the adjoint
+    S, So = SubSampling(600, idx), O.SubSampling(600, idx)
+    y = r.standard_normal(6)
+    assert np.array_equal(S(x), So.matvec(x)) and np.array_equal(S.adjoint(y), So.rmatvec(y))
+    for axis in (0, 1):
+        ia = [0, 2, 7]
+        S, So = SubSampling(600, ia, shape=(20, 30), axis=axis), O.SubSampling(600, ia, shape=(20, 30), axis=axis)
+        y = S(x)
+        assert np.array_equal(y, So.matvec(x)) and np.array_equal(S.adjoint(y), So.rmatvec(y))
+    # empty mask / empty input
+    M = Masking(10, np.zeros(10, bool))
+    assert M(np.arange(10.)).size == 0 and np.array_equal(M.adjoint(np.zeros(0)), np.zeros(10))
+
+
+@pytest.mark.parametrize('dtype,tol', DT)
+def test_prox_and_projections(dtype, tol):
+    from pycsou_b200.func import penalty as P, loss as L
+    r = rng(6)
+    n = 4001
+    x = r.standard_normal(n).astype(dtype)
+    x64 = x.astype(np.float64)
+    for tau in (0.05, 0.7, 3.0):
+        assert rel_l2(P.L1Norm(n).prox(x, tau), O.L1Norm(n).prox(x64, tau)) < tol
+        assert rel_l2(P.L2Norm(n).prox(x, tau * 20), O.L2Norm(n).prox(x64, tau * 20)) < tol
+        assert rel_l2((0.3 * P.L1Norm(n)).fenchel_prox(x, tau), (0.3 * O.L1Norm(n)).fenchel_prox(x64, tau)) < tol
+        y = r.standard_normal(n).astype(dtype)
+        assert rel_l2(L.L1Loss(n, y).prox(x, tau), O.PreCompShift(O.L1Norm(n), y.astype(np.float64)).prox(x64, tau)) < 10 * tol
+        assert rel_l2(L.L2BallLoss(n, y, radius=2.).prox(x, tau),
+                      O.PreCompShift(O.L2Ball(n, 2.), y.astype(np.float64)).prox(x64, tau)) < 10 * tol
+    m = 2000
+    z = r.standard_normal(2 * m).astype(dtype)
+    z[:5] = 0
+    z[m:m + 5] = 0          # zero groups: 1 - tau/0 -> -inf -> 0
+    g = np.tile(np.arange(m), 2)
+    f, fo = P.L21Norm(2 * m, g), O.TVL21Norm(2 * m, m)
+    assert isinstance(f, P.L21Norm)
+    assert rel_l2(f.prox(z, 0.4), fo.prox(z.astype(np.float64), 0.4)) < tol
+    assert abs(f(z) - fo(z.astype(np.float64))) < 1e3 * tol * fo(z.astype(np.float64))
+    assert rel_l2((0.1 * f).fenchel_prox(z, 0.5), (0.1 * fo).fenchel_prox(z.astype(np.float64), 0.5)) < 10 * tol
+    # arbitrary (non-planes) equal-size groups
+    gi = np.repeat(np.arange(m), 2)
+    f2, f2o = P.L21Norm(2 * m, gi), O.L21Norm(2 * m, gi)
+    assert rel_l2(f2.prox(z, 0.4), f2o.prox(z.astype(np.float64), 0.4)) < tol
+    assert np.array_equal(P.NonNegativeOrthant(n).prox(x, 1), O.NonNegativeOrthant(n).prox(x, 1))
+    assert np.array_equal(P.Segment(n, -0.5, 0.2).prox(x, 1), O.Segment(n, -0.5, 0.2).prox(x, 1))
+    assert P.NonNegativeOrthant(n)(x) == np.inf and P.NonNegativeOrthant(n)(np.abs(x)) == 0
+    assert P.Segment(n, -9, 9)(x) == 0 and P.Segment(n, 0, 1)(x) == np.inf
+    assert abs(P.L1Norm(n)(x) - np.sum(np.abs(x64))) < 1e3 * tol * n
+    assert abs(P.SquaredL2Norm(n)(x) - np.sum(x64 ** 2)) < 1e3 * tol * n
+
+
+@pytest.mark.parametrize('dtype,tol', DT)
+def test_loss_gradient_and_composition(dtype, tol):
+    from pycsou_b200.func.loss import SquaredL2Loss
+    from pycsou_b200.linop.conv import Convolve2D
+    r = rng(7)
+    shape = (40, 37)
+    n = shape[0] * shape[1]
+    h = r.random((5, 7))
+    y, x = r.standard_normal(n).astype(dtype), r.standard_normal(n).astype(dtype)
+    A = Convolve2D(n, h, shape, dtype=np.dtype(dtype).name)
+    A.lipschitz_cst = A.diff_lipschitz_cst = 3.0
+    F = (1 / 2) * SquaredL2Loss(dim=n, data=y) * A
+    Fo = O.HalfSquaredL2Loss(y.astype(np.float64), O.Convolve2D(n, h, shape), G_lipschitz=3.0)
+    assert F.diff_lipschitz_cst == Fo.diff_lipschitz_cst == 9.0
+    assert rel_l2(F.gradient(x), Fo.gradient(x.astype(np.float64))) < 20 * tol
+    assert abs(F(x) - Fo(x.astype(np.float64))) < 1e3 * tol * Fo(x.astype(np.float64))
+
+
+def test_lipschitz_power_iteration():
+    from pycsou_b200.linop.diff import FirstDerivative, Gradient
+    D = FirstDerivative(10, kind='forward')
+    D.compute_lipschitz_cst(tol=1e-10, maxiter=5000)
+    assert abs(D.lipschitz_cst - O.power_iteration_lipschitz(O.FirstDerivative(10), 5000)) < 1e-6
+    G = Gradient((64, 64), kind='forward')
+    G.compute_lipschitz_cst(tol=1e-6)
+    assert 2.7 < G.lipschitz_cst <= np.sqrt(8.) + 1e-9
+
+
+def test_torch_in_torch_out_and_errors():
+    from pycsou_b200.linop.diff import Gradient
+    G = Gradient((8, 8), kind='forward')
+    x = torch.arange(64, dtype=torch.float64, device='cuda')
+    y = G(x)
+    assert isinstance(y, torch.Tensor) and y.is_cuda and y.shape == (128,)
+    assert isinstance(G * x, torch.Tensor)
+    with pytest.raises(ValueError):
+        from pycsou_b200 import _kernels as K
+        K.grad2d(x, x, 8, 8, 'forward', True, 1, 1)     # aliased stencil output

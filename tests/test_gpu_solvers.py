@@ -1,0 +1,217 @@
+"""GPU parity of the solvers: pycsou_b200 (through the public, reference-shaped API) vs the golden fixtures produced by
+the reference classes and vs the numpy oracle.  Written the way a reference user would write the script.
+
+Tolerances (BASELINE.json north_star): fp64 iterates <= 1e-10 relative L2; fp32 objective <= 1e-4 relative.
+Each case runs twice: fused kernels allowed, and forced op-by-op (``fused=False``).
+"""
+import numpy as np
+import pytest
+
+from pycsou_b200.util import synth
+from tests import oracle_cases as C
+from tests.helpers import load_golden, rel_l2
+
+pytestmark = pytest.mark.gpu
+TOL64 = 1e-10
+SQRT8 = np.sqrt(8.)
+
+
+def _imports():
+    from pycsou_b200.func.loss import L1Loss, SquaredL2Loss
+    from pycsou_b200.func.penalty import L1Norm, L21Norm, NonNegativeOrthant, Segment
+    from pycsou_b200.linop.conv import Convolve1D, Convolve2D
+    from pycsou_b200.linop.diff import FirstDerivative, Gradient
+    from pycsou_b200.linop.sampling import DownSampling
+    from pycsou_b200.opt.proxalgs import APGD, CPS, DRS, FBS, PDS
+    return locals()
+
+
+def tv_K(shape, kind='forward', dtype='float64'):
+    from pycsou_b200.linop.diff import Gradient
+    K = Gradient(shape=shape, kind=kind, edge=True, dtype=dtype)
+    K.lipschitz_cst = K.diff_lipschitz_cst = SQRT8
+    return K
+
+
+@pytest.mark.parametrize('fused', [True, False])
+@pytest.mark.parametrize('acc,ks', [('CD', (1, 2, 10, 100, 500)), ('BT', (1, 10, 100)), (None, (1, 10, 100))])
+def test_c1_lasso_apgd(acc, ks, fused):
+    m = _imports()
+    meta, g = load_golden('c1_lasso_apgd')
+    truth, h, y = synth.spikes_1d(4096, 32, 0)
+    N = y.size
+    Gop = m['Convolve1D'](size=N, filter=h)
+    lam = 0.1 * np.max(np.abs(Gop.adjoint(y)))
+    assert np.isclose(lam, meta['lam'], rtol=1e-12)
+    for k in ks:
+        F = (1 / 2) * m['SquaredL2Loss'](dim=N, data=y) * Gop
+        G = lam * m['L1Norm'](dim=N)
+        s = m['APGD'](dim=N, F=F, G=G, tau=1.0, acceleration=acc, beta=1.0, max_iter=k - 1, min_iter=k - 1,
+                      accuracy_threshold=0, verbose=None, d=75., fused=fused)
+        est, conv, diag = s.iterate()
+        assert s.iter == k and conv is True
+        assert rel_l2(est['iterand'], g[f'x_{acc}_k{k}']) < TOL64
+    assert rel_l2(est['past_aux'], g[f'aux_{acc}_k{ks[-1]}']) < TOL64
+    assert np.isclose(est['past_t'], float(g[f't_{acc}_k{ks[-1]}']), rtol=1e-15)
+    ri = np.asarray(diag['Relative Improvement'], dtype=float)
+    assert list(diag.columns) == ['Iter', 'Relative Improvement']
+    assert ri[0] == np.inf and np.allclose(ri[1:], g[f'relimp_{acc}'][1:], rtol=1e-7)
+
+
+@pytest.mark.parametrize('fused', [True, False])
+def test_c2_tv_denoise_pds_fp64(fused):
+    m = _imports()
+    meta, g = load_golden('c2_tv_denoise_pds')
+    shape = tuple(meta['shape'])
+    _, y = synth.tv_denoise_problem(shape, 0.1, 0)
+    N = y.size
+    groups = np.tile(np.arange(N), 2)
+    for k in (1, 2, 10, 50):
+        F = (1 / 2) * m['SquaredL2Loss'](dim=N, data=y)
+        s = m['PDS'](dim=N, F=F, H=meta['lam'] * m['L21Norm'](dim=2 * N, groups=groups), K=tv_K(shape), max_iter=k - 1,
+                     min_iter=k - 1, accuracy_threshold=0, verbose=None, fused=fused)
+        assert np.isclose(s.tau, meta['tau'], rtol=1e-15) and s.sigma == s.tau and s.rho == 0.9
+        est, _, diag = s.iterate()
+        assert s.iter == k
+        assert rel_l2(est['primal_variable'], g[f'x_k{k}']) < TOL64
+        assert rel_l2(est['dual_variable'], g[f'z_k{k}']) < TOL64
+    # reference stop rule with the default max_iter/min_iter/threshold: same iteration count, same iterate
+    F = (1 / 2) * m['SquaredL2Loss'](dim=N, data=y)
+    s = m['PDS'](dim=N, F=F, H=meta['lam'] * m['L21Norm'](dim=2 * N, groups=groups), K=tv_K(shape), verbose=None,
+                 fused=fused)
+    est, _, diag = s.iterate()
+    assert s.iter == meta['n_updates_stop'] and len(diag) == s.iter
+    assert rel_l2(est['primal_variable'], g['x_stop']) < TOL64 and rel_l2(est['dual_variable'], g['z_stop']) < TOL64
+    assert list(diag.columns) == ['Iter', 'Relative Improvement (primal variable)',
+                                  'Relative Improvement (dual variable)']
+    rp = np.asarray(diag['Relative Improvement (primal variable)'], dtype=float)
+    rd = np.asarray(diag['Relative Improvement (dual variable)'], dtype=float)
+    assert rp[0] == np.inf and rd[0] == np.inf
+    assert np.allclose(rp[1:], g['relimp_primal'][1:], rtol=1e-7) and np.allclose(rd[1:], g['relimp_dual'][1:], rtol=1e-7)
+
+
+@pytest.mark.parametrize('fused', [True, False])
+@pytest.mark.parametrize('name', ['c2_tv_denoise_pds_nonneg', 'c2_tv_denoise_pds_segment', 'c2_aniso_tv_centered_pds'])
+def test_c2_variants(name, fused):
+    m = _imports()
+    meta, g = load_golden(name)
+    shape = tuple(meta['shape'])
+    _, y = synth.tv_denoise_problem(shape, 0.1, 0)
+    N = y.size
+    for k in (1, 10, 50):
+        F = (1 / 2) * m['SquaredL2Loss'](dim=N, data=y)
+        if name.endswith('nonneg'):
+            kw = dict(G=m['NonNegativeOrthant'](dim=N), H=0.1 * m['L21Norm'](2 * N, np.tile(np.arange(N), 2)), K=tv_K(shape))
+        elif name.endswith('segment'):
+            kw = dict(G=m['Segment'](dim=N, a=0.1, b=0.7), H=0.1 * m['L21Norm'](2 * N, np.tile(np.arange(N), 2)),
+                      K=tv_K(shape))
+        else:
+            kw = dict(H=0.1 * m['L1Norm'](dim=2 * N), K=tv_K(shape, 'centered'))
+        s = m['PDS'](dim=N, F=F, max_iter=k - 1, min_iter=k - 1, accuracy_threshold=0, verbose=None, fused=fused, **kw)
+        est, _, _ = s.iterate()
+        assert rel_l2(est['primal_variable'], g[f'x_k{k}']) < TOL64
+        assert rel_l2(est['dual_variable'], g[f'z_k{k}']) < TOL64
+
+
+def _deconv_solver(m, shape, psf, y, lam, k, dtype, fused):
+    N = y.size
+    A = m['Convolve2D'](size=N, filter=psf, shape=shape, dtype=dtype)
+    F = (1 / 2) * m['SquaredL2Loss'](dim=N, data=y.astype(dtype)) * A
+    return m['PDS'](dim=N, F=F, G=m['NonNegativeOrthant'](dim=N),
+                    H=lam * m['L21Norm'](2 * N, np.tile(np.arange(N), 2)), K=tv_K(shape, dtype=dtype), beta=1.0,
+                    max_iter=k - 1, min_iter=k - 1, accuracy_threshold=0, verbose=None, dtype=dtype, fused=fused)
+
+
+@pytest.mark.parametrize('fused', [True, False])
+@pytest.mark.parametrize('tag', ['sep', 'nonsep'])
+def test_c3_tv_deconv_pds_fp64(tag, fused):
+    m = _imports()
+    meta, g = load_golden(f'c3_tv_deconv_pds_{tag}')
+    shape = tuple(meta['shape'])
+    psf = synth.gaussian_psf_2d(15, 2.5) if tag == 'sep' else synth.rotated_gaussian_psf_2d(15)
+    _, h, y = synth.tv_deconv_problem(shape, psf, 0.02, 0)
+    for k in (1, 2, 10, 50):
+        s = _deconv_solver(m, shape, h, y, meta['lam'], k, 'float64', fused)
+        assert np.isclose(s.tau, meta['tau'], rtol=1e-15)
+        est, _, _ = s.iterate()
+        assert rel_l2(est['primal_variable'], g[f'x_k{k}']) < TOL64
+        assert rel_l2(est['dual_variable'], g[f'z_k{k}']) < TOL64
+
+
+@pytest.mark.parametrize('fused', [True, False])
+@pytest.mark.parametrize('tag', ['sep', 'nonsep'])
+def test_c3_tv_deconv_pds_fp32_objective(tag, fused):
+    m = _imports()
+    meta, g = load_golden(f'c3_tv_deconv_pds_{tag}')
+    shape = tuple(meta['shape'])
+    psf = synth.gaussian_psf_2d(15, 2.5) if tag == 'sep' else synth.rotated_gaussian_psf_2d(15)
+    _, h, y = synth.tv_deconv_problem(shape, psf, 0.02, 0)
+    s = _deconv_solver(m, shape, h, y, meta['lam'], 50, 'float32', fused)
+    est, _, _ = s.iterate()
+    assert est['primal_variable'].dtype == np.float32
+    obj = C.c3_objective(est['primal_variable'].astype(np.float64), tag)
+    assert abs(obj - meta['objective_k50']) <= 1e-4 * abs(meta['objective_k50'])
+
+
+@pytest.mark.parametrize('fused', [True, False])
+def test_examples_rst_pds(fused):
+    """doc/general/examples.rst:19-47 verbatim (explicit Lipschitz constants as in the fixture)."""
+    m = _imports()
+    meta, g = load_golden('examples_pbp_pds')
+    x = np.repeat([0, 2, 1, 3, 0, 2, 0], 10)
+    D = m['FirstDerivative'](size=x.size, kind='forward')
+    D.lipschitz_cst = D.diff_lipschitz_cst = 2.0
+    Gop = m['DownSampling'](size=x.size, downsampling_factor=3)
+    Gop.lipschitz_cst = Gop.diff_lipschitz_cst = 1.0
+    y = Gop(x)
+    l22_loss = (1 / 2) * m['SquaredL2Loss'](dim=Gop.shape[0], data=y)
+    F = l22_loss * Gop
+    H = 0.1 * m['L1Norm'](dim=D.shape[0])
+    G = 0.01 * m['L1Norm'](dim=Gop.shape[1])
+    pds = m['PDS'](dim=Gop.shape[1], F=F, G=G, H=H, K=D, verbose=None, fused=fused)
+    est, converged, diag = pds.iterate()
+    assert pds.iter == meta['n_updates'] and np.isclose(pds.tau, meta['tau'], rtol=1e-15)
+    assert rel_l2(est['primal_variable'], g['x']) < TOL64 and rel_l2(est['dual_variable'], g['z']) < TOL64
+
+
+@pytest.mark.parametrize('fused', [True, False])
+def test_cps_drs_fbs(fused):
+    m = _imports()
+    meta, g = load_golden('misc_cps_drs_fbs')
+    shape = tuple(meta['shape'])
+    N = shape[0] * shape[1]
+    _, y = synth.tv_denoise_problem(shape, 0.1, 1)
+    for k in (1, 10, 40):
+        kw = dict(max_iter=k - 1, min_iter=k - 1, accuracy_threshold=0, verbose=None, fused=fused)
+        s = m['CPS'](dim=N, G=m['L1Loss'](dim=N, data=y), H=0.3 * m['L21Norm'](2 * N, np.tile(np.arange(N), 2)),
+                     K=tv_K(shape), **kw)
+        est, _, _ = s.iterate()
+        assert rel_l2(est['primal_variable'], g[f'cps_x_k{k}']) < TOL64
+        assert rel_l2(est['dual_variable'], g[f'cps_z_k{k}']) < TOL64
+        s = m['DRS'](dim=N, G=m['L1Loss'](dim=N, data=y), H=m['Segment'](dim=N, a=0.2, b=0.6), tau=0.7, **kw)
+        est, _, _ = s.iterate()
+        assert rel_l2(est['primal_variable'], g[f'drs_x_k{k}']) < TOL64
+        assert rel_l2(est['dual_variable'], g[f'drs_z_k{k}']) < TOL64
+        s = m['FBS'](dim=N, F=(1 / 2) * m['SquaredL2Loss'](dim=N, data=y), G=0.2 * m['L1Norm'](dim=N), **kw)
+        est, _, diag = s.iterate()
+        assert est['dual_variable'] is None and list(diag.columns) == ['Iter', 'Relative Improvement (primal variable)']
+        assert rel_l2(est['primal_variable'], g[f'fbs_x_k{k}']) < TOL64
+
+
+def test_iterates_generator_and_torch_output():
+    import torch
+    m = _imports()
+    shape = (24, 32)
+    N = shape[0] * shape[1]
+    _, y = synth.tv_denoise_problem(shape, 0.1, 1)
+    F = (1 / 2) * m['SquaredL2Loss'](dim=N, data=y)
+    mk = lambda **kw: m['PDS'](dim=N, F=F, H=0.1 * m['L21Norm'](2 * N, np.tile(np.arange(N), 2)), K=tv_K(shape),
+                               verbose=None, **kw)
+    s = mk()
+    its = [it['primal_variable'].clone() for it in s.iterates(5)]
+    s2 = mk(max_iter=4, min_iter=4, accuracy_threshold=0)
+    est, _, _ = s2.iterate()
+    assert rel_l2(its[-1].cpu().numpy(), est['primal_variable']) < 1e-14
+    s3 = mk(max_iter=4, min_iter=4, accuracy_threshold=0, x0=torch.zeros(N, dtype=torch.float64, device='cuda'))
+    est3, _, _ = s3.iterate()
+    assert isinstance(est3['primal_variable'], torch.Tensor) and est3['primal_variable'].is_cuda
