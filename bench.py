@@ -1,0 +1,365 @@
+#!/usr/bin/env python
+"""bench.py -- PDS iterations/sec and effective HBM GB/s on the 4096^2 TV-deconvolution workload (BASELINE.json).
+
+Contract (one JSON line on stdout, printed by rank 0):
+
+* a *step* is one solve: ``--iters`` (default 100) Condat-Vu updates of one synthetic ``--size``^2 TV-deconvolution
+  problem (Convolve2D 15x15 PSF + Gradient/L21 + NonNegativeOrthant; BASELINE.json configs[2]).
+* ``value``: iterations/sec with the observation ``y`` already resident in HBM and the iterates staying there
+  (CUDA events around the K timed steps, max over ranks).
+* ``e2e``: the same metric through the public API with HOST buffers: every step copies ``y`` host->device, runs the
+  solve and copies the primal and dual iterates back (wall clock, max over ranks).
+* ``roofline``: algorithmic bytes per iteration (7*N*s) / measured time of one iteration, against the
+  measured HBM copy bandwidth in MEASURED_PEAKS.json.
+* ``cpu_baseline``: the numpy oracle port of the reference path timed on this host (rank 0, N=1) on a bounded sample.
+* ``--impl reference``: the CPU reference arm (oracle port; the pure-Python reference cannot travel to the GPU box).
+
+Working set per iteration (x, y, z in/out: 7 arrays of N*s bytes = 470 MB fp32 / 940 MB fp64 at 4096^2) is larger
+than the 126 MB L2, so no explicit L2 flush is needed between iterations.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+LAMBDA = 0.02
+NOISE = 0.02
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument('--gpus', type=int, default=1)
+    p.add_argument('--steps', type=int, default=5)
+    p.add_argument('--warmup', type=int, default=3)
+    p.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    p.add_argument('--size', type=int, default=4096, help='image is size x size per GPU slab')
+    p.add_argument('--iters', type=int, default=100, help='PDS updates per step (one solve)')
+    p.add_argument('--dtype', default='f32', choices=['f32', 'f64'])
+    p.add_argument('--psf', default='sep', choices=['sep', 'nonsep'])
+    p.add_argument('--no-cpu-baseline', action='store_true')
+    p.add_argument('--no-secondary', action='store_true', help='skip the fp64 / kernel-only secondary measurements')
+    p.add_argument('--cpu-size', type=int, default=0, help='CPU sample image size (default: --size)')
+    p.add_argument('--cpu-iters', type=int, default=2, help='CPU reference updates per sample')
+    return p.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------ clocks sampler
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons every 200 ms while the timed region runs."""
+    FIELDS = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+              'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+              'clocks_event_reasons.sw_power_cap')
+    NAMES = ('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap')
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', '-i', str(self.index), f'--query-gpu={self.FIELDS}', '--format=csv,noheader,nounits',
+                 '-lms', '200'], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return self
+        self.thread = threading.Thread(target=self._pump, daemon=True)
+        self.thread.start()
+        return self
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(',')])
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])), mx.append(float(r[1]))
+                pw.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, flag in zip(self.NAMES, r[3:7]):
+                if flag.lower().startswith('active'):
+                    reasons.add(name)
+        if not sm:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['no samples']}
+        return {'sm_mhz': float(np.median(sm)), 'sm_max_mhz': float(max(mx)), 'power_w_max': float(max(pw)),
+                'samples': len(sm), 'reasons': sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------ workload
+def np_dt(tag):
+    return np.float32 if tag == 'f32' else np.float64
+
+
+def make_problem(size, psf_kind, rank=0):
+    """Synthetic observation of the rank's image (seed = rank: independent problems across ranks)."""
+    from pycsou_b200.util import synth
+    psf = synth.gaussian_psf_2d(15, 2.5) if psf_kind == 'sep' else synth.rotated_gaussian_psf_2d(15)
+    _, psf, y = synth.tv_deconv_problem((size, size), psf, NOISE, seed=rank, dtype=np.float64)
+    return psf, y
+
+
+def make_solver(y, psf, size, tdtype, iters, output):
+    """The reference-facing construction (doc/general/examples.rst:19-47 pattern) for configs[2]."""
+    from pycsou_b200.func.loss import SquaredL2Loss
+    from pycsou_b200.func.penalty import L21Norm, NonNegativeOrthant, tv_groups
+    from pycsou_b200.linop.conv import Convolve2D
+    from pycsou_b200.linop.diff import Gradient
+    from pycsou_b200.opt.proxalgs import PDS
+    N = size * size
+    A = Convolve2D(size=N, filter=psf, shape=(size, size))
+    K = Gradient(shape=(size, size), kind='forward')
+    K.lipschitz_cst = K.diff_lipschitz_cst = float(np.sqrt(8.))
+    F = (1 / 2) * SquaredL2Loss(dim=N, data=y) * A
+    H = LAMBDA * L21Norm(dim=2 * N, groups=tv_groups(N))
+    return PDS(dim=N, F=F, G=NonNegativeOrthant(dim=N), H=H, K=K, beta=1.0, max_iter=iters - 1, min_iter=iters - 1,
+               accuracy_threshold=0, verbose=None, dtype=tdtype, output=output)
+
+
+def algorithmic_bytes_per_iter(size, itemsize):
+    """read x, y, z(2N); write x, z(2N) = 7*N*s."""
+    return 7 * size * size * itemsize
+
+
+def hbm_peak():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    try:
+        with open(path) as f:
+            return float(json.load(f)['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+    except Exception:
+        return 6650.0, 'fallback (B200_PROFILING.md 6.65 TB/s)'
+
+
+# ------------------------------------------------------------------------------------------------ CPU reference
+def cpu_reference_sample(size, psf, y, iters):
+    """``iters`` Condat-Vu updates of the numpy oracle port (reference path restated; fp64 as the reference computes).
+
+    Returns (seconds, threads).  The path is numpy ufuncs + scipy.signal fftconvolve: effectively single threaded.
+    """
+    from oracle import np_oracle as O            # checker / CPU baseline only -- never on the product path
+    N = size * size
+    Fo = O.HalfSquaredL2Loss(y, O.Convolve2D(N, psf, (size, size)), G_lipschitz=1.0)
+    Ho = LAMBDA * O.TVL21Norm(2 * N, N)
+    Ko = O.Gradient((size, size), kind='forward')
+    t0 = time.perf_counter()
+    O.pds_iterate(N, F=Fo, G=O.NonNegativeOrthant(N), H=Ho, K=Ko, K_lipschitz=np.sqrt(8.), beta=1.0,
+                  max_iter=iters - 1, min_iter=iters - 1, accuracy_threshold=0)
+    return time.perf_counter() - t0, 1
+
+
+def reference_arm(args, rank, world):
+    """CPU reference arm: rank 0 only; each step = a bounded sample (--cpu-iters updates) of the same workload."""
+    if rank != 0:
+        return
+    size = args.cpu_size or args.size
+    psf, y = make_problem(size, args.psf, 0)
+    for _ in range(args.warmup):
+        cpu_reference_sample(size, psf, y, 1)
+    t = 0.0
+    for _ in range(args.steps):
+        dt, cores = cpu_reference_sample(size, psf, y, args.cpu_iters)
+        t += dt
+    ips = args.steps * args.cpu_iters / t
+    sample = f'{args.cpu_iters} PDS updates of the {size}x{size} fp64 problem per step (warm-up steps: 1 update each)'
+    line = {
+        'impl': 'reference', 'metric': 'pds_iterations_per_sec', 'value': ips, 'unit': 'iter/s', 'n_gpus': args.gpus,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * t / args.steps, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+        'config': {'workload': f'TV-deconvolution {size}x{size}, Convolve2D 15x15 {args.psf} PSF + Gradient/L21 + '
+                               'NonNegativeOrthant, Condat-Vu PDS (BASELINE.json configs[2])',
+                   'iters_per_step': args.cpu_iters, 'cpu': _cpu_model(), 'numpy': np.__version__},
+        'cpu_baseline': {'value': ips, 'unit': 'iter/s', 'cores': cores, 'kind': 'port', 'sample': sample},
+        'e2e': {'value': ips, 'unit': 'iter/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def _cpu_model():
+    try:
+        with open('/proc/cpuinfo') as f:
+            for ln in f:
+                if ln.startswith('model name'):
+                    return f"{ln.split(':', 1)[1].strip()} x{os.cpu_count()}"
+    except OSError:
+        pass
+    return f'unknown x{os.cpu_count()}'
+
+
+# ------------------------------------------------------------------------------------------------ B200 arm
+def b200_arm(args, rank, local_rank, world):
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise RuntimeError('bench.py needs a CUDA device (no CPU fallback on the product path)')
+    torch.cuda.set_device(local_rank)
+    from pycsou_b200 import _lib
+    _lib.lib()                                                    # fails loudly if libpcsb200.so is missing
+    tdt = torch.float32 if args.dtype == 'f32' else torch.float64
+    size, iters, N = args.size, args.iters, args.size * args.size
+    itemsize = 4 if args.dtype == 'f32' else 8
+
+    psf, y64 = make_problem(size, args.psf, rank)
+    y_host = torch.from_numpy(y64.astype(np_dt(args.dtype))).pin_memory()
+    y_dev = y_host.to('cuda', non_blocking=True)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident: y and the iterates stay in HBM ----
+    solver = make_solver(y_dev, psf, size, tdt, iters, 'torch')
+    for _ in range(args.warmup):
+        solver.reset()
+        solver.iterate()
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = _lib.launch_count
+    ev0.record()
+    for _ in range(args.steps):
+        solver.reset()
+        est, _, _ = solver.iterate()
+    ev1.record()
+    barrier()
+    launches = _lib.launch_count - launches0
+    dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    plan = type(solver._plan).__name__ if getattr(solver, '_plan', None) is not None else 'generic (op-by-op)'
+    checksum = float(est['primal_variable'].double().sum().item())
+
+    # ---- end to end: host y in, host x and z out, every step ----
+    def e2e_step():
+        s = make_solver(y_host, psf, size, tdt, iters, 'numpy')
+        out, _, _ = s.iterate()
+        return out
+    for _ in range(min(args.warmup, 3)):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out = e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    clocks = sampler.stop() if sampler is not None else None
+    assert out['primal_variable'].shape == (N,) and out['dual_variable'].shape == (2 * N,)
+
+    total_iters = world * args.steps * iters
+    ips = total_iters / (dev_ms * 1e-3)
+    ms_iter = dev_ms / (args.steps * iters)
+    peak, peak_src = hbm_peak()
+    alg = algorithmic_bytes_per_iter(size, itemsize)
+    achieved = alg / (ms_iter * 1e-3) / 1e9
+    line = {
+        'metric': 'pds_iterations_per_sec', 'value': ips, 'unit': 'iter/s', 'n_gpus': world, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': dev_ms / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': args.dtype, 'data': 'synthetic',
+        'config': {'workload': f'TV-deconvolution {size}x{size} per GPU, Convolve2D 15x15 {args.psf} PSF + '
+                               'Gradient/L21 + NonNegativeOrthant, Condat-Vu PDS (BASELINE.json configs[2])',
+                   'iters_per_step': iters, 'ms_per_iteration': ms_iter, 'solver_path': plan,
+                   'parallelism': 'one independent image per GPU' if world > 1 else 'single GPU',
+                   'l2_policy': f'working set {alg / 1e6:.0f} MB per iteration > 126 MB L2 (no flush needed)',
+                   'effective_gbs_per_gpu': achieved, 'checksum_x': checksum},
+        'e2e': {'value': total_iters / e2e_s, 'unit': 'iter/s', 'h2d_bytes_per_step': N * itemsize,
+                'd2h_bytes_per_step': 3 * N * itemsize, 'ms_per_step': 1e3 * e2e_s / args.steps},
+        'gpu_launches': launches,
+        'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+                     'traffic': None, 'peak_source': peak_src, 'algorithmic_bytes': alg,
+                     'per': 'one PDS iteration (all kernels of the update)'},
+        'clocks': clocks,
+    }
+    if rank == 0:
+        if world == 1 and not args.no_secondary:
+            line['secondary'] = secondary_measurements(args, psf, y64, torch)
+        if world == 1 and not args.no_cpu_baseline:
+            csize = args.cpu_size or size
+            cpsf, cy = (psf, y64) if csize == size else make_problem(csize, args.psf, 0)
+            cpu_reference_sample(csize, cpsf, cy, 1)                              # warm-up (fft plans, page faults)
+            dt, cores = cpu_reference_sample(csize, cpsf, cy, args.cpu_iters)
+            line['cpu_baseline'] = {'value': args.cpu_iters / dt, 'unit': 'iter/s', 'cores': cores, 'kind': 'port',
+                                    'sample': f'{args.cpu_iters} PDS updates of the {csize}x{csize} fp64 problem '
+                                              f'(numpy oracle port, {_cpu_model()})'}
+        print(json.dumps(line), flush=True)
+
+
+def secondary_measurements(args, psf, y64, torch):
+    """Other precision of the same workload (device-resident iterations/sec); reported, not the headline."""
+    out = {}
+    other = 'f64' if args.dtype == 'f32' else 'f32'
+    tdt = torch.float64 if other == 'f64' else torch.float32
+    isz = 8 if other == 'f64' else 4
+    y_dev = torch.from_numpy(y64.astype(np_dt(other))).to('cuda')
+    solver = make_solver(y_dev, psf, args.size, tdt, args.iters, 'torch')
+    for _ in range(2):
+        solver.reset()
+        solver.iterate()
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    reps = 3
+    for _ in range(reps):
+        solver.reset()
+        solver.iterate()
+    ev1.record()
+    torch.cuda.synchronize()
+    ms_iter = ev0.elapsed_time(ev1) / (reps * args.iters)
+    gbs = algorithmic_bytes_per_iter(args.size, isz) / (ms_iter * 1e-3) / 1e9
+    peak, _ = hbm_peak()
+    out[other] = {'iter_per_s': 1e3 / ms_iter, 'ms_per_iteration': ms_iter, 'effective_gbs': gbs,
+                  'roofline_frac': gbs / peak}
+    return out
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    if args.impl == 'reference':
+        reference_arm(args, rank, world)
+        return
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
+    try:
+        b200_arm(args, rank, local_rank, world)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

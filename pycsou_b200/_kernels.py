@@ -275,5 +275,7 @@ def mask_to_indices(mask_u8: torch.Tensor) -> torch.Tensor:
     _lib.call('pcs_mask_count', ptr(mask_u8), n, ptr(ws), ptr(total), stream())
     m = int(total.item())
     idx = torch.empty(m, dtype=torch.int64, device=mask_u8.device)
+    if m == 0:
+        return idx
     _lib.call('pcs_mask_indices', ptr(mask_u8), n, ptr(ws), ptr(idx), stream())
     return idx

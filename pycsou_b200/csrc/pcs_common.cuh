@@ -106,13 +106,17 @@ template <> __device__ __forceinline__ double tsqrt<double>(double v) { return s
 template <typename T> __device__ __forceinline__ T tmax(T a, T b) { return a > b ? a : b; }
 template <typename T> __device__ __forceinline__ T tmin(T a, T b) { return a < b ? a : b; }
 
+// product rounded on its own (never contracted into an FMA)
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+
 // ---- proximal maps exactly as the reference evaluates them -------------------------------------------------------
 // L1: LpNorm.prox with the l-infinity ball (func/base.py:239-240, math/prox.py:253-256): x - tau*clip(x/tau,-1,1)
 template <typename T> __device__ __forceinline__ T prox_l1(T x, T tau) {
     T q = x / tau;
     q = q > T(1) ? T(1) : q;
     q = q < T(-1) ? T(-1) : q;
-    return x - tau * q;
+    return x - mul_rn(tau, q);   // separately rounded product (no FMA): |x| < tau must cancel as it does in numpy
 }
 // group shrink factor of L21Norm.prox (func/penalty.py:554): clip(1 - tau/||g||, 0); ||g||==0 -> 1-inf -> 0
 template <typename T> __device__ __forceinline__ T l21_factor(T nrm, T tau) {
