@@ -106,6 +106,30 @@ int64_t pcs_mask_workspace_bytes(int64_t n);
 int pcs_mask_count(const void* mask_u8, int64_t n, void* workspace, void* total_out_i64, void* stream);
 int pcs_mask_indices(const void* mask_u8, int64_t n, const void* workspace, void* idx_out_i64, void* stream);
 
+/* ---- fused Condat-Vu (PDS) total-variation iteration: one launch = PrimalDualSplitting.update_iterand +
+ *      update_diagnostics (pycsou/opt/proxalgs.py:343-394) for
+ *        F = 1/2||A x - y||^2 (func/loss.py:165-219 through core/map.py:596-610), G, H = lam*L21Norm | lam*L1Norm
+ *        (func/penalty.py:480-560, 194-245 through core/functional.py:207, 253-265), K = Gradient(kind='forward')
+ *        (linop/diff.py:777-882).
+ *   x, z -> x_out, z_out (ping-pong, no aliasing); z = [d/daxis0 plane ; d/daxis1 plane], each H_loc x W.
+ *   Rows [row_begin, row_end) of the local H_loc x W array are updated; local row 0 is global row grow0 of an image
+ *   with Hg rows (slab decomposition: halo rows live in the local array; single GPU: H_loc = Hg, grow0 = 0).
+ *   data_mode 0: F = None; 1: g = x - b (b = y); 2: g = (A^T A) x - b with b = A^T y and A^T A given as the separable
+ *   autocorrelation taps crow/ccol (HOST arrays of ntaps doubles, ntaps odd <= 29) plus the corner corrections `edge`
+ *   (DEVICE, 4 blocks [left,right,top,bottom] of 14 x 14, sizes nl,nr,nt,nb) of the zero "same" boundary; 3: g = b.
+ *   g_mode 0 none, 1 NonNegativeOrthant, 2 Segment[g_a,g_b], 3 L1 with threshold g_a.  h_mode 0 L21 (isotropic), 1 L1.
+ *   strip_cols / nseg: launch geometry overrides (0 = automatic).  use_tma: 0 plain staging, 1 TMA when the image is
+ *   16-byte aligned, 2 require TMA.  diag_out_f64[4] = ||x'-x||^2, ||x||^2, ||z'-z||^2, ||z||^2 (deterministic).
+ *   workspace: pcs_pds_tv_workspace_bytes() bytes, zero-initialised once. */
+int64_t pcs_pds_tv_workspace_bytes(void);
+PCS_DECL_REAL(pcs_pds_tv_step,
+              (void* x_out, void* z_out, const void* x, const void* z, const void* b, int64_t H_loc, int64_t W,
+               int64_t row_begin, int64_t row_end, int64_t grow0, int64_t Hg, int data_mode, int ntaps,
+               const double* crow_host, const double* ccol_host, const void* edge, int nl, int nr, int nt, int nb,
+               int g_mode, double g_a, double g_b, int h_mode, double lam, double tau, double sigma, double rho,
+               double step0, double step1, int strip_cols, int nseg, int use_tma, void* diag_out_f64, void* workspace,
+               void* stream))
+
 #ifdef __cplusplus
 }
 #endif

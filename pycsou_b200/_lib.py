@@ -48,6 +48,9 @@ REAL = {
     'pcs_conv2d_direct_adj': [P, P, P, I32, I32, I32, I32, I64, I64, P],
     'pcs_conv2d_sep_fwd': [P, P, P, P, I32, I32, I32, I32, P, I64, I64, P],
     'pcs_conv2d_sep_adj': [P, P, P, P, I32, I32, I32, I32, P, I64, I64, P],
+    # fused Condat-Vu TV iteration (csrc/pcs_pds.cu); argument order as in include/pcsb200.h
+    'pcs_pds_tv_step': [P] * 5 + [I64] * 6 + [I32, I32, P, P, P] + [I32] * 4 + [I32, F64, F64, I32] + [F64] * 6 +
+                       [I32] * 3 + [P, P, P],
 }
 PLAIN = {
     'pcs_take': ([P, P, P, I64, I64, I64, I64, I32, P], I32),
@@ -56,6 +59,7 @@ PLAIN = {
     'pcs_mask_indices': ([P, I64, P, P, P], I32),
     'pcs_mask_workspace_bytes': ([I64], I64),
     'pcs_reduce_workspace_bytes': ([], I64),
+    'pcs_pds_tv_workspace_bytes': ([], I64),
     'pcs_version': ([], I32),
     'pcs_num_sms': ([], I32),
 }

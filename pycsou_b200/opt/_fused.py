@@ -1,8 +1,244 @@
-"""Fused-iteration planner (filled in as fused kernels land)."""
+"""Fused-iteration planner: maps a solver's ``(F, G, H, K)`` onto the single-kernel iteration of ``csrc/pcs_pds.cu``.
+
+``plan_pds(solver)`` inspects the expression trees exactly as the reference composes them
+(``(1/2) * SquaredL2Loss(dim, y) * A`` -> ``DiffMapComp(DiffMapComp(HomothetyMap(.5), DiffMapShifted(SquaredL2Norm)), A)``,
+``core/map.py:534-610``; ``lam * L21Norm`` -> ``ProxFuncPostComp``, ``core/functional.py:244-265``) and returns a plan whose
+``step(x, z, diag_row)`` performs one whole ``PrimalDualSplitting.update_iterand`` + ``update_diagnostics``
+(``opt/proxalgs.py:343-394``) in ONE kernel launch, or ``None`` when the problem is not a total-variation problem of
+the supported shape (the solver then runs op by op on the stand-alone kernels).
+
+Supported:  K = Gradient(2-D shape, kind='forward');  H = [lam *] L21Norm (TV groups) or [lam *] L1Norm (anisotropic);
+G in {None, NonNegativeOrthant, Segment, [lam *] L1Norm};  F in {None, (1/2) SquaredL2Loss, (1/2) SquaredL2Loss * A}.
+With ``A`` a separable ``Convolve2D`` (PSF up to 15 x 15) the data-term gradient is evaluated inside the kernel as
+``(A^T A) x - A^T y`` where ``A^T A`` is the separable autocorrelation filter with exact corner corrections for the
+zero "same" boundary (``composite_filter``) and ``A^T y`` is computed once per solve.  Any other differentiable F has
+its gradient computed by the stand-alone kernels and handed to the fused primal/dual kernel.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from numbers import Number
+
+import numpy as np
+import torch
+
+from .. import _kernels as K
+from .. import _lib
+from .._array import to_device
+
+MAX_HL = 14                      # PDS_MAXHL in csrc/pcs_pds.cu
+DM_NONE, DM_IDENTITY, DM_CONV, DM_GIVEN = 0, 1, 2, 3
+GM_NONE, GM_NONNEG, GM_SEGMENT, GM_L1 = 0, 1, 2, 3
+HM_L21, HM_L1 = 0, 1
+
+
+def composite_filter(h, off):
+    """Autocorrelation form of ``T^T T`` for the 1-D zero-"same" convolution ``(T x)[i] = sum_k h[k] x[i + off - k]``.
+
+    Returns ``(c, E_lo, E_hi)``: ``c`` (2 nh - 1 symmetric taps) such that away from the ends ``(T^T T x)[i] =
+    sum_d c[d] x[i - (nh - 1) + d]``, and the corner blocks with ``T^T T = Toeplitz(c) - E_lo (+) E_hi`` where
+    ``E_lo`` (``off`` x ``off``) acts on the first and ``E_hi`` (``nh-1-off`` squared) on the last coordinates.
+    They exist because ``T x`` is truncated to the signal support before ``T^T`` is applied.
+    """
+    h = np.asarray(h, dtype=np.float64).reshape(-1)
+    nh = h.size
+    c = np.correlate(h, h, mode='full')                       # c[d + nh - 1] = sum_m h[m] h[m + d]
+    n_lo, n_hi = int(off), int(nh - 1 - off)
+    E_lo = np.zeros((n_lo, n_lo))
+    for a in range(n_lo):
+        for b in range(n_lo):                                  # terms with output index k < 0: m < off - a
+            E_lo[a, b] = sum(h[m] * h[m + a - b] for m in range(0, off - a) if 0 <= m + a - b < nh)
+    E_hi = np.zeros((n_hi, n_hi))
+    for a in range(n_hi):                                      # a, b count from the first corrected coordinate n - n_hi
+        for b in range(n_hi):                                  # terms with output index k > n - 1: m > off + n_hi - 1 - a
+            E_hi[a, b] = sum(h[m] * h[m + a - b] for m in range(off + n_hi - a, nh) if 0 <= m + a - b < nh)
+    return c, E_lo, E_hi
+
+
+class _Match:
+    """Result of pattern matching; raises ``_NoMatch`` when a piece is unsupported."""
+
+
+class _NoMatch(Exception):
+    pass
+
+
+def _match_K(Kop, dim):
+    from ..linop.diff import GradientOperator
+    if not isinstance(Kop, GradientOperator) or Kop.kind != 'forward' or len(Kop.array_shape) != 2:
+        raise _NoMatch('K is not a 2-D forward-difference Gradient')
+    H, W = Kop.array_shape
+    if H * W != dim or H < 2 or W < 2:
+        raise _NoMatch('shape mismatch')
+    return H, W, Kop.steps
+
+
+def _scaled(f):
+    """Peel ``lam * f`` (ProxFuncPostComp with zero shift) -> (f, lam)."""
+    from ..core.functional import ProxFuncPostComp
+    lam = 1.0
+    while isinstance(f, ProxFuncPostComp):
+        if f.shift != 0 or not isinstance(f.scale, Number):
+            raise _NoMatch('shifted functional')
+        lam *= float(f.scale)
+        f = f.prox_func
+    return f, lam
+
+
+def _match_H(Hf, N):
+    from ..func.penalty import L1Norm, L21Norm
+    f, lam = _scaled(Hf)
+    if type(f) is L21Norm and f._is_planes and f.n_comp == 2 and f.n_groups == N:
+        return HM_L21, lam
+    if type(f) is L1Norm and f.dim == 2 * N:
+        return HM_L1, lam
+    raise _NoMatch('H is not a TV penalty')
+
+
+def _match_G(Gf, tau):
+    from ..func.base import IndicatorFunctional, NullProximableFunctional
+    from ..func.penalty import L1Norm
+    if isinstance(Gf, NullProximableFunctional):
+        return GM_NONE, 0.0, 0.0
+    if isinstance(Gf, IndicatorFunctional) and Gf.kind == 'nonneg':
+        return GM_NONNEG, 0.0, 0.0
+    if isinstance(Gf, IndicatorFunctional) and Gf.kind == 'segment':
+        return GM_SEGMENT, float(Gf.params[0]), float(Gf.params[1])
+    f, lam = _scaled(Gf)
+    if type(f) is L1Norm:
+        return GM_L1, tau * lam, 0.0
+    raise _NoMatch('G has no fused prox')
+
+
+def _half_sq_loss(F):
+    """``(1/2) * SquaredL2Loss(dim, y)`` -> y (host or device array), else None."""
+    from ..core.map import DiffMapComp, DiffMapShifted
+    from ..func.penalty import SquaredL2Norm
+    from ..linop.base import HomothetyMap
+    if not (isinstance(F, DiffMapComp) and isinstance(F.map1, HomothetyMap) and F.map1.cst == 0.5):
+        return None
+    inner = F.map2
+    if not (isinstance(inner, DiffMapShifted) and type(inner.map) is SquaredL2Norm):
+        return None
+    s = inner.shift
+    if isinstance(s, Number):
+        return None
+    return -s if isinstance(s, torch.Tensor) else -np.asarray(s)
+
+
+def _match_F(F, shape):
+    """-> (data_mode, y or None, conv operator or None)."""
+    from ..core.map import DiffMapComp
+    from ..func.base import NullDifferentiableFunctional
+    from ..linop.conv import Convolve2DOperator
+    if isinstance(F, NullDifferentiableFunctional):
+        return DM_NONE, None, None
+    y = _half_sq_loss(F)
+    if y is not None:
+        return DM_IDENTITY, y, None
+    if isinstance(F, DiffMapComp) and isinstance(F.map2, Convolve2DOperator):
+        y = _half_sq_loss(F.map1)
+        A = F.map2
+        if (y is not None and A.is_separable and A.array_shape == tuple(shape)
+                and max(A.filter.shape) - 1 <= MAX_HL and A.filter.shape[0] + 0 <= shape[0]
+                and A.filter.shape[1] <= shape[1]):
+            return DM_CONV, y, A
+    return DM_GIVEN, None, None
+
+
+class PdsTvPlan:
+    """One-launch-per-iteration Condat-Vu TV solver state (device buffers, filter taps, workspace)."""
+
+    def __init__(self, solver, H, W, steps, data_mode, y, A, g, h):
+        self.solver = solver
+        self.H, self.W, self.steps = H, W, steps
+        self.data_mode = data_mode
+        self.g_mode, self.g_a, self.g_b = g
+        self.h_mode, self.lam = h
+        dt = solver._dtype
+        self.dtype = dt
+        self.sfx = '_f32' if dt == torch.float32 else '_f64'
+        dev = K_device()
+        self.ntaps = 1
+        self.crow = self.ccol = None
+        self.edge = None
+        self.nl = self.nr = self.nt = self.nb = 0
+        self.b = None
+        if data_mode == DM_IDENTITY:
+            self.b = to_device(y, dt)
+        elif data_mode == DM_CONV:
+            ccol, Et, Eb = composite_filter(A.hcol, A.offset[0])
+            crow, El, Er = composite_filter(A.hrow, A.offset[1])
+            n = max(ccol.size, crow.size)
+
+            def centred(c):
+                out = np.zeros(n)
+                p = (n - c.size) // 2
+                out[p:p + c.size] = c
+                return out
+            self.ntaps = n
+            self.crow = np.ascontiguousarray(centred(crow))
+            self.ccol = np.ascontiguousarray(centred(ccol))
+            pack = np.zeros((4, MAX_HL, MAX_HL))
+            for k, E in enumerate((El, Er, Et, Eb)):
+                pack[k, :E.shape[0], :E.shape[1]] = E
+            self.nl, self.nr, self.nt, self.nb = El.shape[0], Er.shape[0], Et.shape[0], Eb.shape[0]
+            self.edge = to_device(pack.reshape(-1), dt)
+            self.b = A._adjoint(to_device(y, dt))           # A^T y, once per solve
+        nbytes = int(_lib.call_plain('pcs_pds_tv_workspace_bytes'))
+        self.ws = torch.zeros(nbytes // 8, dtype=torch.float64, device=dev)
+        self._xbuf, self._zbuf = [None, None], [None, None]
+        self.strip_cols = int(os.environ.get('PCS_PDS_STRIP_COLS', '0'))
+        self.nseg = int(os.environ.get('PCS_PDS_NSEG', '0'))
+        self.use_tma = int(os.environ.get('PCS_PDS_TMA', '1'))
+        if self.b is not None and self.b.numel() != H * W:
+            raise _NoMatch('data size mismatch')
+
+    def _out(self, pool, like):
+        for k in (0, 1):
+            if pool[k] is None:
+                pool[k] = torch.empty_like(like)
+            if pool[k].data_ptr() != like.data_ptr():
+                return pool[k]
+        raise RuntimeError('no free ping-pong buffer')
+
+    def step(self, x, z, drow):
+        s = self.solver
+        if self.data_mode == DM_GIVEN:
+            b = s.F._gradient(x)
+        else:
+            b = self.b
+        xo, zo = self._out(self._xbuf, x), self._out(self._zbuf, z)
+        crow = self.crow.ctypes.data_as(C.c_void_p) if self.crow is not None else None
+        ccol = self.ccol.ctypes.data_as(C.c_void_p) if self.ccol is not None else None
+        _lib.call('pcs_pds_tv_step' + self.sfx, xo.data_ptr(), zo.data_ptr(), x.data_ptr(), z.data_ptr(), K.ptr(b),
+                  self.H, self.W, 0, self.H, 0, self.H, self.data_mode, self.ntaps, crow, ccol, K.ptr(self.edge),
+                  self.nl, self.nr, self.nt, self.nb, self.g_mode, self.g_a, self.g_b, self.h_mode, self.lam,
+                  float(s.tau), float(s.sigma), float(s.rho), self.steps[0], self.steps[1], self.strip_cols, self.nseg,
+                  self.use_tma, drow.data_ptr(), self.ws.data_ptr(), K.stream())
+        return xo, zo
+
+
+def K_device():
+    from .._array import device
+    return device()
 
 
 def plan_pds(solver):
-    return None
+    """Fused plan for a ``PrimalDualSplitting`` instance, or None (generic op-by-op path)."""
+    if not solver._H or solver._dtype not in (torch.float32, torch.float64):
+        return None
+    try:
+        H, W, steps = _match_K(solver.K, solver.dim)
+        h = _match_H(solver.H, H * W)
+        g = _match_G(solver.G, float(solver.tau))
+        data_mode, y, A = _match_F(solver.F, (H, W))
+        if not (float(solver.tau) > 0 and float(solver.sigma) > 0):
+            raise _NoMatch('non-positive step')
+        return PdsTvPlan(solver, H, W, steps, data_mode, y, A, g, h)
+    except _NoMatch:
+        return None
 
 
 def plan_apgd(solver):
