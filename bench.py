@@ -112,28 +112,33 @@ def np_dt(tag):
 
 
 def make_problem(size, psf_kind, rank=0):
-    """Synthetic observation of the rank's image (seed = rank: independent problems across ranks)."""
+    """Synthetic observation of the rank's size x size row block (seed = rank, so a block is the same for any GPU
+    count)."""
     from pycsou_b200.util import synth
     psf = synth.gaussian_psf_2d(15, 2.5) if psf_kind == 'sep' else synth.rotated_gaussian_psf_2d(15)
     _, psf, y = synth.tv_deconv_problem((size, size), psf, NOISE, seed=rank, dtype=np.float64)
     return psf, y
 
 
-def make_solver(y, psf, size, tdtype, iters, output):
-    """The reference-facing construction (doc/general/examples.rst:19-47 pattern) for configs[2]."""
+def make_solver(y, psf, size, tdtype, iters, output, slab=None):
+    """The reference-facing construction (doc/general/examples.rst:19-47 pattern) for configs[2].
+
+    With ``slab`` (N > 1 GPUs) the image is (world * size) x size, row-decomposed one size x size slab per GPU
+    (configs[4] layout); ``y`` then holds this rank's rows."""
     from pycsou_b200.func.loss import SquaredL2Loss
     from pycsou_b200.func.penalty import L21Norm, NonNegativeOrthant, tv_groups
     from pycsou_b200.linop.conv import Convolve2D
     from pycsou_b200.linop.diff import Gradient
     from pycsou_b200.opt.proxalgs import PDS
-    N = size * size
-    A = Convolve2D(size=N, filter=psf, shape=(size, size))
-    K = Gradient(shape=(size, size), kind='forward')
+    rows = size * (slab.world if slab is not None else 1)
+    N = rows * size
+    A = Convolve2D(size=N, filter=psf, shape=(rows, size))
+    K = Gradient(shape=(rows, size), kind='forward')
     K.lipschitz_cst = K.diff_lipschitz_cst = float(np.sqrt(8.))
     F = (1 / 2) * SquaredL2Loss(dim=N, data=y) * A
     H = LAMBDA * L21Norm(dim=2 * N, groups=tv_groups(N))
     return PDS(dim=N, F=F, G=NonNegativeOrthant(dim=N), H=H, K=K, beta=1.0, max_iter=iters - 1, min_iter=iters - 1,
-               accuracy_threshold=0, verbose=None, dtype=tdtype, output=output)
+               accuracy_threshold=0, verbose=None, dtype=tdtype, output=output, slab=slab)
 
 
 def algorithmic_bytes_per_iter(size, itemsize):
@@ -236,8 +241,13 @@ def b200_arm(args, rank, local_rank, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    slab = None
+    if world > 1:
+        from pycsou_b200.opt.slab import SlabComm
+        slab = SlabComm()
+
     # ---- device-resident: y and the iterates stay in HBM ----
-    solver = make_solver(y_dev, psf, size, tdt, iters, 'torch')
+    solver = make_solver(y_dev, psf, size, tdt, iters, 'torch', slab)
     for _ in range(args.warmup):
         solver.reset()
         solver.iterate()
@@ -254,11 +264,14 @@ def b200_arm(args, rank, local_rank, world):
     launches = _lib.launch_count - launches0
     dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
     plan = type(solver._plan).__name__ if getattr(solver, '_plan', None) is not None else 'generic (op-by-op)'
-    checksum = float(est['primal_variable'].double().sum().item())
+    cs = est['primal_variable'].double().sum().reshape(1)
+    if world > 1:
+        dist.all_reduce(cs)
+    checksum = float(cs.item())
 
     # ---- end to end: host y in, host x and z out, every step ----
     def e2e_step():
-        s = make_solver(y_host, psf, size, tdt, iters, 'numpy')
+        s = make_solver(y_host, psf, size, tdt, iters, 'numpy', slab)
         out, _, _ = s.iterate()
         return out
     for _ in range(min(args.warmup, 3)):
@@ -286,7 +299,10 @@ def b200_arm(args, rank, local_rank, world):
         'config': {'workload': f'TV-deconvolution {size}x{size} per GPU, Convolve2D 15x15 {args.psf} PSF + '
                                'Gradient/L21 + NonNegativeOrthant, Condat-Vu PDS (BASELINE.json configs[2])',
                    'iters_per_step': iters, 'ms_per_iteration': ms_iter, 'solver_path': plan,
-                   'parallelism': 'one independent image per GPU' if world > 1 else 'single GPU',
+                   'parallelism': (f'one {world * size}x{size} image row-decomposed into {world} slabs of {size}x{size}, '
+                                   'halo rows pushed to the neighbour GPUs over NVLink inside the update kernel, '
+                                   'stop-test norms all-reduced; value counts slab-iterations (N x image iterations/s)')
+                   if world > 1 else 'single GPU',
                    'l2_policy': f'working set {alg / 1e6:.0f} MB per iteration > 126 MB L2 (no flush needed)',
                    'effective_gbs_per_gpu': achieved, 'checksum_x': checksum},
         'e2e': {'value': total_iters / e2e_s, 'unit': 'iter/s', 'h2d_bytes_per_step': N * itemsize,
@@ -297,6 +313,9 @@ def b200_arm(args, rank, local_rank, world):
                      'per': 'one PDS iteration (all kernels of the update)'},
         'clocks': clocks,
     }
+    if slab is not None:
+        from pycsou_b200.opt.slab import release_arenas
+        release_arenas()
     if rank == 0:
         if world == 1 and not args.no_secondary:
             line['secondary'] = secondary_measurements(args, psf, y64, torch)

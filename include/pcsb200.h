@@ -130,6 +130,38 @@ PCS_DECL_REAL(pcs_pds_tv_step,
                double step0, double step1, int strip_cols, int nseg, int use_tma, void* diag_out_f64, void* workspace,
                void* stream))
 
+/* ---- slab decomposition of one image over the GPUs of a box (the reference has no multi-device
+ *      path: this is the partitioned form of PrimalDualSplitting.update_iterand, opt/proxalgs.py:343-355) ----------
+ * pcs_pds_tv_step_slab = pcs_pds_tv_step on this rank's rows [row_begin, row_end) of its local H_loc x W arrays (halo
+ * rows included), fused with the halo exchange: rows of x', z' that a row neighbour holds as halo are ALSO stored
+ * into that neighbour's output arrays through NVLink, and the last block releases `epoch` into a flag word of each
+ * neighbour.  Blocks that touch halo rows first acquire epoch-1 on the flag words the neighbours wrote.
+ * peer_desc_host: HOST array of 18 int64
+ *   [0] x_up [1] z_up [2] x_dn [3] z_dn   device pointers to the neighbours' OUTPUT arrays (pcs_peer_open), 0 = none
+ *   [4] plane_up [5] plane_dn             elements per z plane of the neighbour's arrays (its H_loc * W)
+ *   [6] drow_up  [7] drow_dn              neighbour's local row index minus mine, for the same image row
+ *   [8] nx_up [9] nx_dn [10] nz_up [11] nz_dn   my first / last updated rows of x (of z0, z1) that are pushed (<= 16)
+ *   [12] wait_up [13] wait_dn             my uint32 flag words, written by the neighbours
+ *   [14] sig_up  [15] sig_dn              uint32 flag words in the neighbours' memory
+ *   [16] epoch (>= 1, +1 per step on every rank)   [17] device uint32 error word (set if a wait gave up after ~2 s)
+ */
+PCS_DECL_REAL(pcs_pds_tv_step_slab,
+              (void* x_out, void* z_out, const void* x, const void* z, const void* b, int64_t H_loc, int64_t W,
+               int64_t row_begin, int64_t row_end, int64_t grow0, int64_t Hg, int data_mode, int ntaps,
+               const double* crow_host, const double* ccol_host, const void* edge, int nl, int nr, int nt, int nb,
+               int g_mode, double g_a, double g_b, int h_mode, double lam, double tau, double sigma, double rho,
+               double step0, double step1, int strip_cols, int nseg, int use_tma, void* diag_out_f64, void* workspace,
+               void* stream, const int64_t* peer_desc_host))
+
+/* Peer memory (CUDA IPC): the only entry points that own device memory.  A rank allocates its slab arena, publishes
+ * the pcs_peer_handle_bytes()-byte handle, and maps its row neighbours' arenas. */
+int pcs_peer_handle_bytes(void);
+int pcs_peer_alloc(void** dptr_out, int64_t bytes, void* handle_out);   /* zero-initialised */
+int pcs_peer_open(const void* handle, void** dptr_out);
+int pcs_peer_close(void* dptr);
+int pcs_peer_free(void* dptr);
+int pcs_peer_can_access(int device, int peer);                          /* 1 / 0, negative on error */
+
 #ifdef __cplusplus
 }
 #endif

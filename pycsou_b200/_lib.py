@@ -51,6 +51,9 @@ REAL = {
     # fused Condat-Vu TV iteration (csrc/pcs_pds.cu); argument order as in include/pcsb200.h
     'pcs_pds_tv_step': [P] * 5 + [I64] * 6 + [I32, I32, P, P, P] + [I32] * 4 + [I32, F64, F64, I32] + [F64] * 6 +
                        [I32] * 3 + [P, P, P],
+    # ... fused with the halo push / flag handshake of the slab decomposition (last argument: HOST int64[18])
+    'pcs_pds_tv_step_slab': [P] * 5 + [I64] * 6 + [I32, I32, P, P, P] + [I32] * 4 + [I32, F64, F64, I32] + [F64] * 6 +
+                            [I32] * 3 + [P, P, P, P],
 }
 PLAIN = {
     'pcs_take': ([P, P, P, I64, I64, I64, I64, I32, P], I32),
@@ -60,6 +63,13 @@ PLAIN = {
     'pcs_mask_workspace_bytes': ([I64], I64),
     'pcs_reduce_workspace_bytes': ([], I64),
     'pcs_pds_tv_workspace_bytes': ([], I64),
+    # peer (NVLink) memory for the slab-decomposed solvers (csrc/pcs_peer.cu)
+    'pcs_peer_handle_bytes': ([], I32),
+    'pcs_peer_alloc': ([P, I64, P], I32),
+    'pcs_peer_open': ([P, P], I32),
+    'pcs_peer_close': ([P], I32),
+    'pcs_peer_free': ([P], I32),
+    'pcs_peer_can_access': ([I32, I32], I32),
     'pcs_version': ([], I32),
     'pcs_num_sms': ([], I32),
 }
@@ -118,6 +128,13 @@ def call(name: str, *args):
         if rc == 1:
             raise ValueError(msg)
         raise RuntimeError(msg)
+
+
+def check(rc: int):
+    """Raise for a non-zero status returned by a ``call_plain`` entry point."""
+    if rc != 0:
+        msg = lib().pcs_last_error().decode(errors='replace')
+        raise (ValueError if rc == 1 else RuntimeError)(msg)
 
 
 def call_plain(name: str, *args):

@@ -60,9 +60,11 @@ __device__ __forceinline__ void block_sum(double (&v)[K], double* smem /* K * (B
 // Deterministic grid reduction of K partial sums: every block writes its partials to `partials[k*gridDim + block]`,
 // the last block to arrive (atomic ticket) sums them in fixed order into out[0..K) and resets the ticket.
 // `ticket` must be zero before the first launch (workspace is allocated zeroed by the host).
+// Returns (block-uniform) whether this block was the last one.  With `sys_scope` the arrival fence is system wide, so
+// that stores this grid made to PEER memory are ordered before anything the last block publishes afterwards.
 template <int K, int BLOCK>
-__device__ __forceinline__ void grid_sum_finish(double (&v)[K], double* partials, unsigned int* ticket, double* out,
-                                                double* smem) {
+__device__ __forceinline__ bool grid_sum_finish(double (&v)[K], double* partials, unsigned int* ticket, double* out,
+                                                double* smem, bool sys_scope = false) {
     __shared__ bool is_last;
     block_sum<K, BLOCK>(v, smem);
     const int nb = gridDim.x * gridDim.y * gridDim.z;
@@ -70,7 +72,8 @@ __device__ __forceinline__ void grid_sum_finish(double (&v)[K], double* partials
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int k = 0; k < K; ++k) partials[(size_t)k * nb + bid] = v[k];
-        __threadfence();
+        if (sys_scope) __threadfence_system();
+        else __threadfence();
         unsigned int t = atomicAdd(ticket, 1u);
         is_last = (t == (unsigned int)nb - 1);
     }
@@ -91,6 +94,7 @@ __device__ __forceinline__ void grid_sum_finish(double (&v)[K], double* partials
             *ticket = 0u;
         }
     }
+    return is_last;
 }
 
 template <typename T> struct Vec;   // widest aligned vector (16 bytes)

@@ -89,17 +89,26 @@ class _DeviceLoop:
                 break
             new_state = spec if spec is not None else self._step(state, it)
             spec = None
-            self._post_metric_copy(it)
-            if self.verbose is not None and it % self.verbose == 0:
+            show = self.verbose is not None and it % self.verbose == 0
+            # the 32-byte metric of update `it` travels to the host only if the stop test of index it+1 (or the
+            # verbose print) will read it; otherwise nothing sits between two update kernels on the stream and all
+            # rows are fetched in one copy after the loop
+            if show or self.min_iter < it + 1 <= self.max_iter:
+                self._post_metric_copy(it)
+            if show:
                 self._metric_ready(it)
                 self.iter = it
                 print(self._diag_row(it))
             state = new_state
             it += 1
         self.iter = it
-        for k in list(self._diag_events):
-            self._metric_ready(k)
+        self._diag_events.clear()
+        self._reduce_diag(it)
+        self._diag_host[:it].copy_(self._diag_dev[:it])      # synchronous: every update has finished after this
         return state
+
+    def _reduce_diag(self, n):
+        """Hook for distributed solvers: sum the per-rank partial norms of rows [0, n) (single GPU: nothing)."""
 
     def _primal_metric(self, it):
         d = self._diag_host[it]
@@ -118,9 +127,10 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
                  tau: Optional[float] = None, sigma: Optional[float] = None, rho: Optional[float] = None,
                  beta: Optional[float] = None, x0=None, z0=None,
                  max_iter: int = 500, min_iter: int = 10, accuracy_threshold: float = 1e-3, verbose: Optional[int] = 1,
-                 *, dtype=None, output: str = 'auto', fused: bool = True):
+                 *, dtype=None, output: str = 'auto', fused: bool = True, slab=None):
         self.dim = dim
         self._H = True
+        self._slab = slab        # opt/slab.py SlabComm: one image row-decomposed over the GPUs of the process group
         if isinstance(F, DifferentiableMap):
             if F.shape[1] != dim:
                 raise ValueError(f'F does not have the proper dimension: {F.shape[1]}!={dim}.')
@@ -233,6 +243,8 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
     # -- device state ----------------------------------------------------------------------------------------------
     def _init_state(self):
         dt = self._dtype
+        if self._slab is not None:
+            return self._plan.init_state(self._user_x0, self._user_z0)
         x = (torch.zeros(self.dim, dtype=dt, device=device()) if self._user_x0 is None
              else to_device(self._user_x0, dt).clone())
         if self._H is False:
@@ -277,11 +289,38 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
         return self._generic_step(x, z, self._diag_dev[it])
 
     def _make_plan(self):
+        if self._slab is not None:
+            from .slab import SlabPdsTvPlan, make_slab_plan
+            if not isinstance(self._plan, SlabPdsTvPlan):     # the peer arena is collective and expensive: keep it
+                self._plan = make_slab_plan(self, self._slab)
+            return self._plan
         self._plan = None
         if self._allow_fused:
             from ._fused import plan_pds
             self._plan = plan_pds(self)
         return self._plan
+
+    # -- slab decomposition: the norms of the stop test are per-rank partial sums until all-reduced ----------------
+    def _alloc_diag(self):
+        super()._alloc_diag()
+        self._diag_reduced = set()
+
+    def _post_metric_copy(self, it):
+        if self._slab is not None and it not in self._diag_reduced:
+            self._slab.all_reduce_sum(self._diag_dev[it])
+            self._diag_reduced.add(it)
+        super()._post_metric_copy(it)
+
+    def _reduce_diag(self, n):
+        if self._slab is None:
+            return
+        idx = [i for i in range(n) if i not in self._diag_reduced]
+        if idx:
+            sel = torch.tensor(idx, device=self._diag_dev.device)
+            t = self._diag_dev.index_select(0, sel)
+            self._slab.all_reduce_sum(t)
+            self._diag_dev.index_copy_(0, sel, t)
+            self._diag_reduced.update(idx)
 
     # -- public API (reference names) ------------------------------------------------------------------------------
     def _as_output(self, t):
@@ -297,6 +336,9 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
         state = self._init_state() if self.iter == 0 or self.iterand is None else self._state_from_iterand()
         x, z = self._run_loop(state)
         self.converged = True
+        if self._slab is not None:
+            self._plan.check()
+            x, z = self._plan.extract(x, z)          # this rank's rows
         self._state = (x, z)
         self.iterand = {'primal_variable': self._as_output(x), 'dual_variable': self._as_output(z)}
         self.old_iterand = self.iterand
@@ -305,12 +347,16 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
 
     def _state_from_iterand(self):
         it = self.iterand
+        if self._slab is not None:
+            return self._plan.init_state(it['primal_variable'], it['dual_variable'])
         x = to_device(it['primal_variable'], self._dtype)
         z = None if it['dual_variable'] is None else to_device(it['dual_variable'], self._dtype)
         return x, z
 
     def update_iterand(self) -> dict:
         """One update on the current iterand (used by ``iterates(n)``); returns device tensors."""
+        if self._slab is not None:
+            raise NotImplementedError('iterates(n) / update_iterand() are not available in slab mode; use iterate()')
         if self._plan is None and self._allow_fused:
             self._make_plan()
         if self.iter == 0 or self.iterand is None:
