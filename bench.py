@@ -135,7 +135,8 @@ def make_solver(y, psf, size, tdtype, iters, output, slab=None):
     A = Convolve2D(size=N, filter=psf, shape=(rows, size))
     K = Gradient(shape=(rows, size), kind='forward')
     K.lipschitz_cst = K.diff_lipschitz_cst = float(np.sqrt(8.))
-    F = (1 / 2) * SquaredL2Loss(dim=N, data=y) * A
+    data = y if slab is None else slab.layout(rows, size).local(y)
+    F = (1 / 2) * SquaredL2Loss(dim=N, data=data) * A
     H = LAMBDA * L21Norm(dim=2 * N, groups=tv_groups(N))
     return PDS(dim=N, F=F, G=NonNegativeOrthant(dim=N), H=H, K=K, beta=1.0, max_iter=iters - 1, min_iter=iters - 1,
                accuracy_threshold=0, verbose=None, dtype=tdtype, output=output, slab=slab)

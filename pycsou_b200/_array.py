@@ -15,6 +15,20 @@ _NP2T = {np.dtype('float32'): torch.float32, np.dtype('float64'): torch.float64,
          np.dtype('complex64'): torch.complex64, np.dtype('complex128'): torch.complex128}
 
 
+class SlabRows:
+    """This rank's rows of a vector that is defined on the whole (row-decomposed) image -- see ``opt/slab.py``.
+
+    Stands in for the global vector when a functional is built (``SquaredL2Loss(dim=N, data=SlabRows(...))``): it has
+    the global ``size`` for the constructors' shape checks and carries only the local rows.
+    """
+
+    def __init__(self, local, size: int):
+        self.local, self.size = local, int(size)
+
+    def __neg__(self):
+        return SlabRows(-self.local if isinstance(self.local, torch.Tensor) else -np.asarray(self.local), self.size)
+
+
 def torch_dtype(dtype) -> torch.dtype:
     """Map a numpy-style dtype spec ('float64', np.float32, type, torch dtype, None) to a torch dtype."""
     if dtype is None:
@@ -45,6 +59,8 @@ def device():
 
 def to_device(x, dtype: torch.dtype | None = None) -> torch.Tensor:
     """Contiguous flat CUDA tensor holding ``x`` (one H2D copy for host data, no copy for matching device data)."""
+    if isinstance(x, SlabRows):
+        raise NotImplementedError('row-decomposed data can only be used by a solver constructed with slab=SlabComm(...)')
     if isinstance(x, torch.Tensor):
         t = x
         if not t.is_cuda:

@@ -20,7 +20,8 @@ __all__ = ['ProximableLoss', 'DifferentiableLoss', 'L2Loss', 'SquaredL2Loss', 'L
 
 
 def _neg(data):
-    if isinstance(data, torch.Tensor):
+    from .._array import SlabRows
+    if isinstance(data, (torch.Tensor, SlabRows)):
         return -data
     return -np.asarray(data) if not isinstance(data, Number) else -data
 

@@ -124,7 +124,8 @@ def _half_sq_loss(F):
     s = inner.shift
     if isinstance(s, Number):
         return None
-    return -s if isinstance(s, torch.Tensor) else -np.asarray(s)
+    from .._array import SlabRows
+    return -s if isinstance(s, (torch.Tensor, SlabRows)) else -np.asarray(s)
 
 
 def _match_F(F, shape):
@@ -165,6 +166,9 @@ class PdsTvPlan:
         self.edge = None
         self.nl = self.nr = self.nt = self.nb = 0
         self.b = None
+        from .._array import SlabRows
+        if isinstance(y, SlabRows):
+            raise NotImplementedError('row-decomposed data needs a solver constructed with slab=SlabComm(...)')
         if data_mode == DM_IDENTITY:
             self.b = to_device(y, dt)
         elif data_mode == DM_CONV:
@@ -202,6 +206,14 @@ class PdsTvPlan:
             if pool[k].data_ptr() != like.data_ptr():
                 return pool[k]
         raise RuntimeError('no free ping-pong buffer')
+
+    def release(self, *tensors):
+        """The final iterates are handed to the caller: forget them, so that the next solve cannot overwrite them."""
+        for t in tensors:
+            for pool in (self._xbuf, self._zbuf):
+                for k in (0, 1):
+                    if pool[k] is not None and t is not None and pool[k].data_ptr() == t.data_ptr():
+                        pool[k] = None
 
     def step(self, x, z, drow):
         s = self.solver

@@ -49,8 +49,12 @@ class _DeviceLoop:
 
     def _alloc_diag(self):
         rows = int(max(self.max_iter, self.min_iter)) + 2
-        self._diag_dev = torch.zeros(rows, self._n_metrics, dtype=torch.float64, device=device())
-        self._diag_host = torch.zeros(rows, self._n_metrics, dtype=torch.float64).pin_memory()
+        dev = getattr(self, '_diag_dev', None)
+        if dev is not None and dev.shape[0] == rows and dev.device == device():
+            dev.zero_()                      # buffers (one of them pinned) are kept between solves of one solver
+        else:
+            self._diag_dev = torch.zeros(rows, self._n_metrics, dtype=torch.float64, device=device())
+            self._diag_host = torch.zeros(rows, self._n_metrics, dtype=torch.float64).pin_memory()
         self._diag_events = {}
 
     def _post_metric_copy(self, it):
@@ -294,10 +298,14 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
             if not isinstance(self._plan, SlabPdsTvPlan):     # the peer arena is collective and expensive: keep it
                 self._plan = make_slab_plan(self, self._slab)
             return self._plan
-        self._plan = None
-        if self._allow_fused:
-            from ._fused import plan_pds
-            self._plan = plan_pds(self)
+        # a plan captures F's data, the filters and the prox modes; it is rebuilt only when one of them is replaced
+        key = (id(self.F), id(self.G), id(self.H), id(self.K), float(self.tau), self._dtype, self._allow_fused)
+        if getattr(self, '_plan_key', None) != key:
+            self._plan = None
+            if self._allow_fused:
+                from ._fused import plan_pds
+                self._plan = plan_pds(self)
+            self._plan_key = key
         return self._plan
 
     # -- slab decomposition: the norms of the stop test are per-rank partial sums until all-reduced ----------------
@@ -339,6 +347,8 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
         if self._slab is not None:
             self._plan.check()
             x, z = self._plan.extract(x, z)          # this rank's rows
+        elif self._plan is not None:
+            self._plan.release(x, z)
         self._state = (x, z)
         self.iterand = {'primal_variable': self._as_output(x), 'dual_variable': self._as_output(z)}
         self.old_iterand = self.iterand
@@ -380,10 +390,13 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
 
     def _build_diagnostics(self, n):
         from pandas import DataFrame
-        cols = ['Iter', 'Relative Improvement (primal variable)'] + \
-            (['Relative Improvement (dual variable)'] if self._H else [])
-        rows = [self._diag_row(i) for i in range(n)]
-        return DataFrame(rows, columns=cols)
+        d = self._diag_host[:n].numpy()
+        with np.errstate(divide='ignore', invalid='ignore'):
+            rel = np.where(d[:, 1::2] == 0, np.inf, np.sqrt(d[:, 0::2]) / np.sqrt(d[:, 1::2]))
+        data = {'Iter': np.arange(n), 'Relative Improvement (primal variable)': rel[:, 0]}
+        if self._H:
+            data['Relative Improvement (dual variable)'] = rel[:, 1]
+        return DataFrame(data)
 
     def print_diagnostics(self):
         print(dict(self.diagnostics.loc[self.iter]))

@@ -18,7 +18,7 @@ Usage (every rank)::
 
     comm = SlabComm()                                   # default process group
     lay  = comm.layout(Hg, W)                           # this rank's rows: lay.r0, lay.r1
-    F = (1/2) * SquaredL2Loss(dim=Hg*W, data=y[lay.r0:lay.r1].ravel()) * Convolve2D(size=Hg*W, filter=psf, shape=(Hg, W))
+    F = (1/2) * SquaredL2Loss(dim=Hg*W, data=lay.local(y[lay.r0:lay.r1])) * Convolve2D(size=Hg*W, filter=psf, shape=(Hg, W))
     pds = PDS(dim=Hg*W, F=F, G=NonNegativeOrthant(Hg*W), H=lam*L21Norm(...), K=Gradient((Hg, W), kind='forward'),
               slab=comm, ...)
     est, _, diag = pds.iterate()                        # est[...] hold this rank's rows (z: [plane0 rows ; plane1 rows])
@@ -73,6 +73,11 @@ class SlabLayout:
     @property
     def plane(self) -> int:
         return self.H_loc * self.W
+
+    def local(self, rows):
+        """Wrap this rank's rows of an image-sized vector for use as functional data (``SquaredL2Loss(N, data=...)``)."""
+        from .._array import SlabRows
+        return SlabRows(rows, self.Hg * self.W)
 
     def own(self, t: torch.Tensor) -> torch.Tensor:
         """Owned rows (n_own x W view) of a local H_loc x W array."""
@@ -299,7 +304,10 @@ class SlabPdsTvPlan:
         self.nl = self.nr = self.nt = self.nb = 0
         self.b = None
         if data_mode != Fz.DM_NONE:
-            y_own = to_device(y, dt)
+            from .._array import SlabRows
+            if not isinstance(y, SlabRows):
+                raise ValueError('slab mode: pass this rank\'s rows of the data as SlabLayout.local(rows)')
+            y_own = to_device(y.local, dt)
             if y_own.numel() != lay.n_own * W:
                 raise ValueError(f'slab mode: the data must hold this rank\'s {lay.n_own} rows ({lay.n_own * W} values), '
                                  f'got {y_own.numel()}')

@@ -55,7 +55,7 @@ def main():
         tdt = torch.float64 if a.dtype == 'f64' else torch.float32
         K = Gradient(shape=(Hg, W), kind='forward')
         K.lipschitz_cst = K.diff_lipschitz_cst = float(np.sqrt(8.))
-        F = (1 / 2) * SquaredL2Loss(dim=N, data=y[lay.r0:lay.r1].reshape(-1))
+        F = (1 / 2) * SquaredL2Loss(dim=N, data=lay.local(y[lay.r0:lay.r1].reshape(-1)))
         if a.data == 'conv':
             F = F * Convolve2D(size=N, filter=psf, shape=(Hg, W))
         H = 0.05 * L21Norm(dim=2 * N, groups=tv_groups(N))
