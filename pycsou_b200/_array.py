@@ -25,8 +25,31 @@ class SlabRows:
     def __init__(self, local, size: int):
         self.local, self.size = local, int(size)
 
+    @property
+    def shape(self):
+        return (self.size,)
+
     def __neg__(self):
-        return SlabRows(-self.local if isinstance(self.local, torch.Tensor) else -np.asarray(self.local), self.size)
+        return Negated(self)
+
+
+class Negated:
+    """``-a`` with the sign still pending: the losses shift by ``-data`` (reference ``func/loss.py:69,120``), and
+    negating a large host array costs more than the upload -- the sign is applied on the device instead."""
+
+    def __init__(self, a):
+        self.a = a
+
+    @property
+    def shape(self):
+        return tuple(self.a.shape)
+
+    def __neg__(self):
+        return self.a
+
+    def __array__(self, dtype=None, copy=None):
+        v = -np.asarray(self.a)
+        return v if dtype is None else v.astype(dtype)
 
 
 def torch_dtype(dtype) -> torch.dtype:
@@ -61,6 +84,8 @@ def to_device(x, dtype: torch.dtype | None = None) -> torch.Tensor:
     """Contiguous flat CUDA tensor holding ``x`` (one H2D copy for host data, no copy for matching device data)."""
     if isinstance(x, SlabRows):
         raise NotImplementedError('row-decomposed data can only be used by a solver constructed with slab=SlabComm(...)')
+    if isinstance(x, Negated):
+        return -to_device(x.a, dtype)
     if isinstance(x, torch.Tensor):
         t = x
         if not t.is_cuda:

@@ -161,9 +161,6 @@ class Map(ABC):
 
 
 def _shift_size(shift):
-    from .._array import SlabRows
-    if isinstance(shift, SlabRows):
-        return shift.size
     return 1 if isinstance(shift, Number) else int(np.prod(tuple(shift.shape)))
 
 

@@ -20,10 +20,13 @@ __all__ = ['ProximableLoss', 'DifferentiableLoss', 'L2Loss', 'SquaredL2Loss', 'L
 
 
 def _neg(data):
-    from .._array import SlabRows
-    if isinstance(data, (torch.Tensor, SlabRows)):
+    """``-data``; for arrays the sign stays pending until the upload (``_array.Negated``)."""
+    from .._array import Negated, SlabRows
+    if isinstance(data, Number):
         return -data
-    return -np.asarray(data) if not isinstance(data, Number) else -data
+    if isinstance(data, Negated):
+        return data.a
+    return Negated(data if isinstance(data, (torch.Tensor, SlabRows)) else np.asarray(data))
 
 
 def ProximableLoss(func: ProximableFunctional, data) -> ProximableFunctional:

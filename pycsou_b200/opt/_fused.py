@@ -124,7 +124,9 @@ def _half_sq_loss(F):
     s = inner.shift
     if isinstance(s, Number):
         return None
-    from .._array import SlabRows
+    from .._array import Negated, SlabRows
+    if isinstance(s, Negated):
+        return s.a
     return -s if isinstance(s, (torch.Tensor, SlabRows)) else -np.asarray(s)
 
 
