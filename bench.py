@@ -35,6 +35,10 @@ if ROOT not in sys.path:
 
 LAMBDA = 0.02
 NOISE = 0.02
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the fused kernel from the committed `ncu --set full`
+# captures (profiles/r01_ncu_pds_{f32,f64}_v5.txt); bench.py cannot run under ncu itself
+NCU_DRAM_BYTES = {('f32', 4096, 'sep'): 455807232, ('f64', 4096, 'sep'): 962406656}
+NCU_SOURCE = 'profiles/r01_ncu_pds_*_v5.txt (ncu --set full, one launch)'
 
 
 def parse_args():
@@ -310,7 +314,8 @@ def b200_arm(args, rank, local_rank, world):
                 'd2h_bytes_per_step': 3 * N * itemsize, 'ms_per_step': 1e3 * e2e_s / args.steps},
         'gpu_launches': launches,
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                     'traffic': None, 'peak_source': peak_src, 'algorithmic_bytes': alg,
+                     'traffic': NCU_DRAM_BYTES.get((args.dtype, size, args.psf)), 'traffic_source': NCU_SOURCE,
+                     'peak_source': peak_src, 'algorithmic_bytes': alg,
                      'per': 'one PDS iteration (all kernels of the update)'},
         'clocks': clocks,
     }

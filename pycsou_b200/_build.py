@@ -18,7 +18,8 @@ CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libpcsb200.so')
 OBJ_DIR = os.path.join(HERE, 'build')
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
-              '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr', '-Xptxas', '-v']
+              '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr', '-Xptxas', '-v'] + \
+    os.environ.get('PCS_NVCC_EXTRA', '').split()          # e.g. -DPDS_PHASE_TIMING for scripts/probe_phases.py
 
 
 def _nvcc() -> str:
