@@ -2,3 +2,4 @@ from .base import *
 from .conv import *
 from .diff import *
 from .sampling import *
+from .transform import *

@@ -215,3 +215,55 @@ def test_iterates_generator_and_torch_output():
     s3 = mk(max_iter=4, min_iter=4, accuracy_threshold=0, x0=torch.zeros(N, dtype=torch.float64, device='cuda'))
     est3, _, _ = s3.iterate()
     assert isinstance(est3['primal_variable'], torch.Tensor) and est3['primal_variable'].is_cuda
+
+
+def _c4_solver(shape, mask, y, lam, eps, k, dtype='complex128', output='numpy'):
+    """BASELINE.json configs[3] exactly as tests/golden/gen_golden.py:c4_csmri builds it with the reference classes."""
+    from pycsou_b200.func.base import ProxFuncHStack
+    from pycsou_b200.func.loss import L2BallLoss
+    from pycsou_b200.func.penalty import L21Norm
+    from pycsou_b200.linop.base import LinOpVStack
+    from pycsou_b200.linop.sampling import Masking
+    from pycsou_b200.linop.transform import DFT2
+    from pycsou_b200.opt.proxalgs import CPS
+    N = shape[0] * shape[1]
+    M = Masking(size=N, sampling_bool=mask, dtype=dtype)
+    m = M.shape[0]
+    MF = M * DFT2(shape, dtype=dtype)
+    MF.lipschitz_cst = MF.diff_lipschitz_cst = 1.0
+    Kop = LinOpVStack(MF, tv_K(shape, dtype=dtype))
+    H = ProxFuncHStack(L2BallLoss(dim=m, data=y, radius=eps), lam * L21Norm(2 * N, np.tile(np.arange(N), 2)))
+    return CPS(dim=N, G=None, H=H, K=Kop, tau=1 / 3, sigma=1 / 3, rho=1, x0=np.zeros(N, dtype=dtype),
+               z0=np.zeros(m + 2 * N, dtype=dtype), max_iter=k - 1, min_iter=k - 1, accuracy_threshold=0,
+               verbose=None, output=output), m
+
+
+def test_c4_csmri_cps_complex128():
+    """Compressed-sensing MRI: K = [Mask * DFT ; Gradient], H = [L2-ball data term ; TV], ChambollePock (complex)."""
+    meta, g = load_golden('c4_csmri_cps')
+    shape = tuple(meta['shape'])
+    mask, y = g['mask'].astype(bool), g['y']
+    for k in (1, 5, 20):
+        s, m = _c4_solver(shape, mask, y, meta['lam'], meta['eps'], k)
+        assert m == meta['m']                                   # sampling mask bit-exact: same sample count and order
+        est, _, _ = s.iterate()
+        assert np.iscomplexobj(est['primal_variable'])
+        assert rel_l2(est['primal_variable'], g[f'x_k{k}']) < TOL64
+        assert rel_l2(est['dual_variable'], g[f'z_k{k}']) < TOL64
+
+
+def test_c4_csmri_cps_complex64_vs_oracle():
+    shape = (64, 96)
+    N = shape[0] * shape[1]
+    rng = np.random.default_rng(11)
+    truth = synth.phantom(shape).reshape(-1) * np.exp(1j * 2 * np.pi * (np.arange(N) / N))
+    mask = rng.random(N) < 0.3
+    m = int(mask.sum())
+    y = np.fft.fft2(truth.reshape(shape), norm='ortho').reshape(-1)[mask] + 0.01 * (
+        rng.standard_normal(m) + 1j * rng.standard_normal(m))
+    lam, eps, k = 0.05, 0.01 * np.sqrt(2 * m), 30
+    s, _ = _c4_solver(shape, mask, y.astype(np.complex64), lam, eps, k, dtype='complex64')
+    est, _, _ = s.iterate()
+    xo, zo, _, _ = C.c4(k, mask, y, shape=shape, lam=lam, eps=eps)
+    assert est['primal_variable'].dtype == np.complex64
+    assert rel_l2(est['primal_variable'], xo) < 2e-4 and rel_l2(est['dual_variable'], zo) < 2e-4
