@@ -47,7 +47,11 @@ def parse_args():
     p.add_argument('--steps', type=int, default=5)
     p.add_argument('--warmup', type=int, default=3)
     p.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    p.add_argument('--workload', default='c3', choices=['c3', 'c5'],
+                   help="c3: BASELINE configs[2], one size^2 slab per GPU (weak scaling; the default and the metric's "
+                        "config); c5: BASELINE configs[4], ONE 32768^2 image row-decomposed over the GPUs (strong scaling)")
     p.add_argument('--size', type=int, default=4096, help='image is size x size per GPU slab')
+    p.add_argument('--c5-size', type=int, default=32768, help='side of the c5 image')
     p.add_argument('--iters', type=int, default=100, help='PDS updates per step (one solve)')
     p.add_argument('--dtype', default='f32', choices=['f32', 'f64'])
     p.add_argument('--psf', default='sep', choices=['sep', 'nonsep'])
@@ -336,6 +340,153 @@ def b200_arm(args, rank, local_rank, world):
         print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------------------------------------------ C5 (strong scaling)
+def c5_rows_on_device(Hg, W, r0, r1, psf, tdt, torch):
+    """Rows [r0, r1) of the synthetic Hg x W observation, built on the device: piecewise-constant phantom, blurred by
+    the 15x15 PSF (this package's Convolve2D on the rows plus a 7-row margin), plus noise drawn per 1024-row block from
+    a generator seeded with the block index -- the image is the same for every GPU count."""
+    from pycsou_b200.linop.conv import Convolve2D
+    R = 7
+    lo, hi = max(r0 - R, 0), min(r1 + R, Hg)
+    r = (torch.arange(lo, hi, device='cuda', dtype=torch.float64) / Hg)[:, None]
+    c = (torch.arange(W, device='cuda', dtype=torch.float64) / W)[None, :]
+    img = torch.zeros(hi - lo, W, dtype=tdt, device='cuda')
+    img.masked_fill_((r >= 0.10) & (r < 0.45) & (c >= 0.15) & (c < 0.40), 0.8)
+    img.masked_fill_((r >= 0.55) & (r < 0.90) & (c >= 0.10) & (c < 0.30), 0.4)
+    img.masked_fill_((r >= 0.30) & (r < 0.70) & (c >= 0.55) & (c < 0.90), 0.6)
+    img.masked_fill_(((r - 0.72) ** 2 + (c - 0.50) ** 2) < 0.12 ** 2, 1.0)
+    A = Convolve2D(size=img.numel(), filter=psf, shape=tuple(img.shape))
+    y = A(img.reshape(-1)).view(hi - lo, W)[r0 - lo:r0 - lo + (r1 - r0)].contiguous()
+    del img
+    blk = 1024
+    for b in range(r0 // blk, (r1 - 1) // blk + 1):
+        g = torch.Generator(device='cuda')
+        g.manual_seed(1000 + b)
+        nb = torch.randn(blk, W, generator=g, device='cuda', dtype=torch.float32)
+        g0, g1 = max(r0, b * blk), min(r1, (b + 1) * blk)
+        y[g0 - r0:g1 - r0] += (NOISE * nb[g0 - b * blk:g1 - b * blk]).to(tdt)
+    return y.reshape(-1)
+
+
+def c5_arm(args, rank, local_rank, world):
+    """BASELINE.json configs[4]: ONE c5_size^2 fp32 TV-deconvolution row-decomposed over the GPUs (strong scaling)."""
+    import torch
+    import torch.distributed as dist
+    from pycsou_b200 import _lib
+    from pycsou_b200.func.loss import SquaredL2Loss
+    from pycsou_b200.func.penalty import L21Norm, NonNegativeOrthant, tv_groups
+    from pycsou_b200.linop.conv import Convolve2D
+    from pycsou_b200.linop.diff import Gradient
+    from pycsou_b200.opt.proxalgs import PDS
+    from pycsou_b200.opt.slab import SlabComm, SlabLayout, release_arenas
+    from pycsou_b200.util import synth
+    torch.cuda.set_device(local_rank)
+    _lib.lib()
+    tdt = torch.float32 if args.dtype == 'f32' else torch.float64
+    itemsize = 4 if args.dtype == 'f32' else 8
+    Hg = W = args.c5_size
+    N = Hg * W
+    iters = args.iters
+    psf = synth.gaussian_psf_2d(15, 2.5)
+    slab = SlabComm() if world > 1 else None
+    lay = slab.layout(Hg, W) if slab is not None else SlabLayout(Hg, W, 1, 0)
+    y_dev = c5_rows_on_device(Hg, W, lay.r0, lay.r1, psf, tdt, torch)
+    y_host = torch.empty(y_dev.shape, dtype=tdt, pin_memory=True)
+    y_host.copy_(y_dev)
+    torch.cuda.synchronize()
+
+    def build(y, output):
+        A = Convolve2D(size=N, filter=psf, shape=(Hg, W))
+        K = Gradient(shape=(Hg, W), kind='forward')
+        K.lipschitz_cst = K.diff_lipschitz_cst = float(np.sqrt(8.))
+        F = (1 / 2) * SquaredL2Loss(dim=N, data=y if slab is None else lay.local(y)) * A
+        H = LAMBDA * L21Norm(dim=2 * N, groups=tv_groups(N))
+        return PDS(dim=N, F=F, G=NonNegativeOrthant(dim=N), H=H, K=K, beta=1.0, max_iter=iters - 1,
+                   min_iter=iters - 1, accuracy_threshold=0, verbose=None, dtype=tdt, output=output, slab=slab)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    solver = build(y_dev, 'torch')
+    for _ in range(args.warmup):
+        solver.reset()
+        solver.iterate()
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = _lib.launch_count
+    ev0.record()
+    for _ in range(args.steps):
+        solver.reset()
+        est, _, diag = solver.iterate()
+    ev1.record()
+    barrier()
+    launches = _lib.launch_count - launches0
+    dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    cs = est['primal_variable'].double().sum().reshape(1)
+    if world > 1:
+        dist.all_reduce(cs)
+    rel_last = float(diag['Relative Improvement (primal variable)'].iloc[-1])
+    plan = type(solver._plan).__name__
+    del est, solver
+
+    # end to end: this rank's rows of y from pinned host memory every step; the step's result read back is the
+    # diagnostics table (global, all-reduced) -- the iterates of a 32768^2 problem stay distributed in HBM
+    def e2e_step():
+        s = build(y_host, 'torch')
+        _, _, d = s.iterate()
+        return float(d['Relative Improvement (primal variable)'].iloc[-1])
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        last = e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    clocks = sampler.stop() if sampler is not None else None
+    assert abs(last - rel_last) <= 1e-6 * abs(rel_last) + 1e-12
+    if slab is not None:
+        release_arenas()
+
+    total_iters = args.steps * iters
+    ms_iter = dev_ms / total_iters
+    peak, peak_src = hbm_peak()
+    alg = 7 * N * itemsize
+    achieved = alg / (ms_iter * 1e-3) / 1e9                      # whole job, all GPUs
+    line = {
+        'metric': 'pds_iterations_per_sec', 'value': total_iters / (dev_ms * 1e-3), 'unit': 'iter/s', 'n_gpus': world,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dev_ms / args.steps, 'higher_is_better': True,
+        'scaling': 'strong', 'vs_baseline': None, 'dtype': args.dtype, 'data': 'synthetic',
+        'config': {'workload': f'TV-deconvolution {Hg}x{W} (ONE image), Convolve2D 15x15 sep PSF + Gradient/L21 + '
+                               'NonNegativeOrthant, Condat-Vu PDS (BASELINE.json configs[4])',
+                   'iters_per_step': iters, 'ms_per_iteration': ms_iter, 'solver_path': plan,
+                   'parallelism': f'{world} row slabs of {lay.n_own}x{W}, halo rows pushed over NVLink inside the update '
+                                  'kernel, stop-test norms all-reduced' if world > 1 else 'single GPU',
+                   'l2_policy': f'working set {alg / world / 1e9:.1f} GB per GPU per iteration > 126 MB L2',
+                   'effective_gbs_total': achieved, 'checksum_x': float(cs.item()), 'rel_improvement_last': rel_last},
+        'e2e': {'value': total_iters / e2e_s, 'unit': 'iter/s', 'h2d_bytes_per_step': lay.n_own * W * itemsize,
+                'd2h_bytes_per_step': iters * 32, 'ms_per_step': 1e3 * e2e_s / args.steps,
+                'result_read_back': 'diagnostics table (iterates stay distributed in HBM)'},
+        'gpu_launches': launches,
+        'roofline': {'bound': 'hbm', 'achieved': achieved / world, 'peak': peak, 'unit': 'GB/s',
+                     'frac': achieved / world / peak, 'traffic': None, 'peak_source': peak_src,
+                     'algorithmic_bytes': alg // world, 'per': 'one PDS iteration, per GPU'},
+        'clocks': clocks,
+    }
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
 def secondary_measurements(args, psf, y64, torch):
     """Other precision of the same workload (device-resident iterations/sec); reported, not the headline."""
     out = {}
@@ -379,7 +530,12 @@ def main():
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
         dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
     try:
-        b200_arm(args, rank, local_rank, world)
+        if args.workload == 'c5':
+            if args.iters == 100:
+                args.iters = 50
+            c5_arm(args, rank, local_rank, world)
+        else:
+            b200_arm(args, rank, local_rank, world)
     finally:
         if world > 1:
             import torch.distributed as dist

@@ -4,7 +4,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 import bench
 
-NAMES = ['wait_x', 'hpass', 'sync1(+hcorr)', 'colpass', 'wait_step', 'primal', 'sync2', 'dual', 'sync3']
+NAMES = ['wait_x', 'hpass', 'sync1(+hcorr)', 'colpass', 'wait_step', 'primal', 'sync2', 'dual', 'sync3', 'issue_step', 'issue_x']
 def run(dtype):
     tdt = torch.float32 if dtype == 'f32' else torch.float64
     psf, y64 = bench.make_problem(4096, 'sep', 0)
@@ -25,7 +25,7 @@ def run(dtype):
     order = np.argsort(tot)
     print('   slowest blocks:', order[-8:], tot[order[-8:]].astype(int))
     print('   fastest blocks:', order[:8], tot[order[:8]].astype(int))
-    m = pt[:, :9].mean(0)
+    m = pt[:, :11].mean(0)
     for k, n in enumerate(NAMES):
         print(f'   {n:14s} mean {m[k]:9.0f} cyc  {100 * m[k] / tot.mean():5.1f}%   (max over blocks {pt[:, k].max():9.0f})')
     print(f'   unaccounted (prologue, finish) {100 * (1 - m.sum() / tot.mean()):.1f}%')
