@@ -130,6 +130,20 @@ PCS_DECL_REAL(pcs_pds_tv_step,
                double step0, double step1, int strip_cols, int nseg, int use_tma, void* diag_out_f64, void* workspace,
                void* stream))
 
+/* ---- a whole AcceleratedProximalGradientDescent solve in one launch: the loop of core/solver.py:55-76 with
+ *      update_iterand / update_diagnostics / stopping_metric of opt/proxalgs.py:586-622, for
+ *        F = 1/2||h * x - y||^2 (flat Convolve1D, linop/conv.py:20-164), G = none | g_param-threshold L1 | nonneg.
+ *   One block keeps the problem in shared memory (n <= pcs_apgd_conv1d_run_max_n(); at most 256 taps) and runs updates it0, it0+1, ...
+ *   while (it <= max_iter and ||x'-x||/||x|| > threshold) or it <= min_iter, exactly as the reference does.
+ *   g_mode 0 none, 1 L1 (g_param = tau * lambda), 2 NonNegativeOrthant.  accel 0 none, 1 'BT', 2 'CD' (parameter d).
+ *   x_inout / aux_inout: iterate and past_aux (in: start, out: result).  diag_out_f64: one row of 4 doubles per update
+ *   (||x'-x||^2, ||x||^2, 0, 0).  n_iter_out_i64[0] = update index after the loop, [1] = final t (raw double bits). */
+int64_t pcs_apgd_conv1d_run_max_n(void);
+PCS_DECL_REAL(pcs_apgd_conv1d_run,
+              (void* x_inout, void* aux_inout, const void* y, const void* h, int nh, int offset, int64_t n, int g_mode,
+               double g_param, double tau, int accel, double d, double t0, int64_t it0, int64_t max_iter,
+               int64_t min_iter, double threshold, void* diag_out_f64, void* n_iter_out_i64, void* stream))
+
 /* ---- slab decomposition of one image over the GPUs of a box (the reference has no multi-device
  *      path: this is the partitioned form of PrimalDualSplitting.update_iterand, opt/proxalgs.py:343-355) ----------
  * pcs_pds_tv_step_slab = pcs_pds_tv_step on this rank's rows [row_begin, row_end) of its local H_loc x W arrays (halo

@@ -51,6 +51,8 @@ REAL = {
     # fused Condat-Vu TV iteration (csrc/pcs_pds.cu); argument order as in include/pcsb200.h
     'pcs_pds_tv_step': [P] * 5 + [I64] * 6 + [I32, I32, P, P, P] + [I32] * 4 + [I32, F64, F64, I32] + [F64] * 6 +
                        [I32] * 3 + [P, P, P],
+    # a whole APGD solve (flat Convolve1D data term) in one launch (csrc/pcs_apgd.cu)
+    'pcs_apgd_conv1d_run': [P, P, P, P, I32, I32, I64, I32, F64, F64, I32, F64, F64, I64, I64, I64, F64, P, P, P],
     # ... fused with the halo push / flag handshake of the slab decomposition (last argument: HOST int64[18])
     'pcs_pds_tv_step_slab': [P] * 5 + [I64] * 6 + [I32, I32, P, P, P] + [I32] * 4 + [I32, F64, F64, I32] + [F64] * 6 +
                             [I32] * 3 + [P, P, P, P],
@@ -70,6 +72,7 @@ PLAIN = {
     'pcs_peer_close': ([P], I32),
     'pcs_peer_free': ([P], I32),
     'pcs_peer_can_access': ([I32, I32], I32),
+    'pcs_apgd_conv1d_run_max_n': ([], I64),
     'pcs_version': ([], I32),
     'pcs_num_sms': ([], I32),
 }

@@ -255,5 +255,66 @@ def plan_pds(solver):
         return None
 
 
+class ApgdConv1dPlan:
+    """Whole-solve plan for ``APGD`` with ``F = 1/2 ||h * x - y||^2`` on a flat vector (``csrc/pcs_apgd.cu``)."""
+
+    ACC = {None: 0, 'BT': 1, 'CD': 2}
+
+    def __init__(self, solver, A, y, g_mode, g_param):
+        dt = solver._dtype
+        self.solver, self.dtype = solver, dt
+        self.sfx = '_f32' if dt == torch.float32 else '_f64'
+        self.y = to_device(y, dt)
+        self.h = to_device(A.filter, dt)
+        self.nh, self.offset, self.n = int(A.filter.size), int(A.offset), int(A.n)
+        self.g_mode, self.g_param = g_mode, float(g_param)
+        self.n_iter = torch.zeros(2, dtype=torch.int64, device=K_device())
+
+    def run(self, x, aux, t0, it0, diag_dev, single=False):
+        """Updates ``it0, it0 + 1, ...`` under the reference's loop condition (``single``: exactly update ``it0``);
+        ``diag_dev`` receives one row per update, starting at its first row.  Returns (x, aux, t, iter)."""
+        s = self.solver
+        x, aux = x.clone(), aux.clone()
+        hi, lo, thr = (it0, it0, 0.0) if single else (s.max_iter, s.min_iter, s.accuracy_threshold)
+        _lib.call('pcs_apgd_conv1d_run' + self.sfx, x.data_ptr(), aux.data_ptr(), self.y.data_ptr(), self.h.data_ptr(),
+                  self.nh, self.offset, self.n, self.g_mode, self.g_param, float(s.tau), self.ACC[s.acceleration],
+                  float(s.d), float(t0), int(it0), int(hi), int(lo), float(thr),
+                  diag_dev.data_ptr(), self.n_iter.data_ptr(), K.stream())
+        n_iter, t_bits = (int(v) for v in self.n_iter.cpu())
+        t = float(np.int64(t_bits).view(np.float64))
+        return x, aux, (t if n_iter > it0 else t0), n_iter
+
+
 def plan_apgd(solver):
-    return None
+    """Whole-solve plan for an ``AcceleratedProximalGradientDescent`` instance, or None (generic op-by-op path)."""
+    from ..core.map import DiffMapComp
+    from ..func.base import IndicatorFunctional, NullProximableFunctional
+    from ..func.penalty import L1Norm
+    from ..linop.conv import Convolve1DOperator
+    if solver._dtype not in (torch.float32, torch.float64) or solver.acceleration not in ApgdConv1dPlan.ACC:
+        return None
+    F = solver.F
+    if not (isinstance(F, DiffMapComp) and isinstance(F.map2, Convolve1DOperator)):
+        return None
+    A, y = F.map2, _half_sq_loss(F.map1)
+    from .._array import SlabRows
+    if y is None or isinstance(y, SlabRows) or A.outer != 1 or A.inner != 1 or A.n != solver.dim:
+        return None
+    if A.n > int(_lib.call_plain('pcs_apgd_conv1d_run_max_n')) or A.filter.size > 256:
+        return None
+    if not float(solver.tau) > 0 or int(np.prod(np.shape(y))) != A.n:
+        return None
+    G = solver.G
+    if isinstance(G, NullProximableFunctional):
+        g = (0, 0.0)
+    elif isinstance(G, IndicatorFunctional) and G.kind == 'nonneg':
+        g = (2, 0.0)
+    else:
+        try:
+            f, lam = _scaled(G)
+        except _NoMatch:
+            return None
+        if type(f) is not L1Norm:
+            return None
+        g = (1, float(solver.tau) * lam)
+    return ApgdConv1dPlan(solver, A, y, *g)

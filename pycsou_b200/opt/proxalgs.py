@@ -513,16 +513,18 @@ class AcceleratedProximalGradientDescent(_DeviceLoop, GenericIterativeAlgorithm)
     def _step(self, state, it):
         x, x_old, t_old = state
         if self._plan is not None:
-            t, a = self._next_t(it, t_old)
-            x_new, x_temp = self._plan.step(x, x_old, a, self._diag_dev[it])
+            x_new, x_temp, t, _ = self._plan.run(x, x_old, t_old, it, self._diag_dev[it:], single=True)
             return x_new, x_temp, t
         return self._generic_step(x, x_old, t_old, it, self._diag_dev[it])
 
     def _make_plan(self):
-        self._plan = None
-        if self._allow_fused:
-            from ._fused import plan_apgd
-            self._plan = plan_apgd(self)
+        key = (id(self.F), id(self.G), float(self.tau), self._dtype, self._allow_fused, self.acceleration)
+        if getattr(self, '_plan_key', None) != key:
+            self._plan = None
+            if self._allow_fused:
+                from ._fused import plan_apgd
+                self._plan = plan_apgd(self)
+            self._plan_key = key
         return self._plan
 
     def _as_output(self, t):
@@ -538,7 +540,13 @@ class AcceleratedProximalGradientDescent(_DeviceLoop, GenericIterativeAlgorithm)
         else:
             state = (to_device(self.iterand['iterand'], self._dtype), to_device(self.iterand['past_aux'], self._dtype),
                      self.iterand['past_t'])
-        x, aux, t = self._run_loop(state)
+        if self._plan is not None and hasattr(self._plan, 'run') and self.verbose is None:
+            # the whole loop -- updates, norms and the reference's stop test -- runs inside one kernel
+            self._alloc_diag()
+            x, aux, t, self.iter = self._plan.run(state[0], state[1], state[2], self.iter, self._diag_dev)
+            self._diag_host[:self.iter].copy_(self._diag_dev[:self.iter])
+        else:
+            x, aux, t = self._run_loop(state)
         self.converged = True
         self.iterand = {'iterand': self._as_output(x), 'past_aux': self._as_output(aux), 'past_t': t}
         self.old_iterand = self.iterand
@@ -557,8 +565,7 @@ class AcceleratedProximalGradientDescent(_DeviceLoop, GenericIterativeAlgorithm)
             self._scratch_row = torch.zeros(self._n_metrics, dtype=torch.float64, device=device())
         self._diag_dev = self._scratch_row.reshape(1, -1).expand(1, -1)
         if self._plan is not None:
-            t, a = self._next_t(self.iter, t_old)
-            x, aux = self._plan.step(x, x_old, a, self._scratch_row)
+            x, aux, t, _ = self._plan.run(x, x_old, t_old, self.iter, self._scratch_row, single=True)
         else:
             x, aux, t = self._generic_step(x, x_old, t_old, self.iter, self._scratch_row)
         return {'iterand': x, 'past_aux': aux, 'past_t': t}
@@ -569,7 +576,10 @@ class AcceleratedProximalGradientDescent(_DeviceLoop, GenericIterativeAlgorithm)
 
     def _build_diagnostics(self, n):
         from pandas import DataFrame
-        return DataFrame([self._diag_row(i) for i in range(n)], columns=['Iter', 'Relative Improvement'])
+        d = self._diag_host[:n].numpy()
+        with np.errstate(divide='ignore', invalid='ignore'):
+            rel = np.where(d[:, 1] == 0, np.inf, np.sqrt(d[:, 0]) / np.sqrt(d[:, 1]))
+        return DataFrame({'Iter': np.arange(n), 'Relative Improvement': rel})
 
     def print_diagnostics(self):
         print(dict(self.diagnostics.loc[self.iter]))
