@@ -119,7 +119,8 @@ int pcs_mask_indices(const void* mask_u8, int64_t n, const void* workspace, void
  *   (DEVICE, 4 blocks [left,right,top,bottom] of 14 x 14, sizes nl,nr,nt,nb) of the zero "same" boundary; 3: g = b.
  *   g_mode 0 none, 1 NonNegativeOrthant, 2 Segment[g_a,g_b], 3 L1 with threshold g_a.  h_mode 0 L21 (isotropic), 1 L1.
  *   strip_cols / nseg: launch geometry overrides (0 = automatic).  use_tma: 0 plain staging, 1 TMA when the image is
- *   16-byte aligned, 2 require TMA.  diag_out_f64[4] = ||x'-x||^2, ||x||^2, ||z'-z||^2, ||z||^2 (deterministic).
+ *   16-byte aligned, 2 require TMA, 3 require TMA and the single-role kernel (deconvolution otherwise runs the
+ *   warp-specialised one).  diag_out_f64[4] = ||x'-x||^2, ||x||^2, ||z'-z||^2, ||z||^2 (deterministic).
  *   workspace: pcs_pds_tv_workspace_bytes() bytes, zero-initialised once. */
 int64_t pcs_pds_tv_workspace_bytes(void);
 PCS_DECL_REAL(pcs_pds_tv_step,
