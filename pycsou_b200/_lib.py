@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libpcsb200.so')
+LIB_PATH = os.environ.get('PCS_LIB_PATH') or os.path.join(_HERE, 'libpcsb200.so')   # override: A/B of builds
 
 _lib = None
 launch_count = 0   # number of C-ABI compute calls issued (bench.py reports it as gpu_launches evidence)
