@@ -15,8 +15,8 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
-LIB = os.path.join(HERE, 'libpcsb200.so')
-OBJ_DIR = os.path.join(HERE, 'build')
+LIB = os.environ.get('PCS_BUILD_LIB') or os.path.join(HERE, 'libpcsb200.so')       # override: variant builds for A/B runs
+OBJ_DIR = os.environ.get('PCS_BUILD_OBJ') or os.path.join(HERE, 'build')
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr', '-Xptxas', '-v'] + \
     os.environ.get('PCS_NVCC_EXTRA', '').split()          # e.g. -DPDS_PHASE_TIMING for scripts/probe_phases.py

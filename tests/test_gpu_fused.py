@@ -70,6 +70,9 @@ CASES = [
     ((48, 136), 'sep', 'nonneg', 'l21', 1., (1, 3)),
     ((30, 40), 'sep', 'nonneg', 'l21', 1., (15, 15)),         # image barely larger than the filter support
     ((64, 140), 'nonsep', 'nonneg', 'l21', 1., (5, 5)),       # gradient by stand-alone kernels, fused primal/dual
+    ((72, 256), 'sep', 'nonneg', 'l21', 1., (15, 15)),        # width = whole 128-column strips (no overlap column)
+    ((48, 384), 'identity', 'nonneg', 'l21', 1., None),
+    ((40, 264), 'sep', 'segment', 'l21', 1., (15, 15)),       # last strip narrower than the filter half-width
 ]
 
 
@@ -100,6 +103,19 @@ def test_fused_geometry_and_staging_are_bit_identical(env, monkeypatch):
     _, est, _ = _run(kw, 3, True)
     assert np.array_equal(est['primal_variable'], base['primal_variable'])
     assert np.array_equal(est['dual_variable'], base['dual_variable'])
+
+
+@pytest.mark.parametrize('shape', [(100, 300), (72, 256), (40, 264)])
+def test_fused_single_role_kernel_fp32(shape, monkeypatch):
+    """fp32 deconvolution normally runs the warp-specialised kernel; PCS_PDS_TMA=3 selects the single-role one."""
+    kw = _problem(shape, 'sep', 'nonneg', 'l21', 'float32')
+    _, ref, _ = _run(kw, 3, False)
+    _, ws, _ = _run(kw, 3, True)
+    monkeypatch.setenv('PCS_PDS_TMA', '3')
+    _, est, _ = _run(kw, 3, True)
+    assert rel_l2(est['primal_variable'], ref['primal_variable']) < 2e-5
+    assert rel_l2(est['dual_variable'], ref['dual_variable']) < 2e-5
+    assert rel_l2(est['primal_variable'], ws['primal_variable']) < 2e-6
 
 
 def test_fused_matches_numpy_oracle_directly():
