@@ -47,7 +47,9 @@ def parse_args():
     p.add_argument('--steps', type=int, default=5)
     p.add_argument('--warmup', type=int, default=3)
     p.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    p.add_argument('--workload', default='c3', choices=['c3', 'c5'],
+    p.add_argument('--c4-size', type=int, default=2048, help='side of each c4 (compressed-sensing MRI) image')
+    p.add_argument('--c4-problems', type=int, default=8, help='independent c4 problems per GPU')
+    p.add_argument('--workload', default='c3', choices=['c3', 'c4', 'c5'],
                    help="c3: BASELINE configs[2], one size^2 slab per GPU (weak scaling; the default and the metric's "
                         "config); c5: BASELINE configs[4], ONE 32768^2 image row-decomposed over the GPUs (strong scaling)")
     p.add_argument('--size', type=int, default=4096, help='image is size x size per GPU slab')
@@ -340,6 +342,170 @@ def b200_arm(args, rank, local_rank, world):
         print(json.dumps(line), flush=True)
 
 
+
+# ------------------------------------------------------------------------------------------------ C4 (independent problems)
+C4_LAM, C4_FRAC, C4_NOISE = 0.05, 0.3, 0.01
+
+
+def c4_problem(size, p):
+    """Problem p of BASELINE.json configs[3]: phantom x smooth unit-modulus phase, mask =
+    rng(p).random(N) < 0.3, y = Mask FFT2_ortho(truth) + 0.01 complex noise.  Host arrays (complex128)."""
+    from pycsou_b200.util import synth
+    N = size * size
+    rng = np.random.default_rng(p)
+    mask = rng.random(N) < C4_FRAC
+    truth = synth.phantom((size, size)).reshape(-1) * np.exp(2j * np.pi * (np.arange(N) / N))
+    m = int(mask.sum())
+    y = np.fft.fft2(truth.reshape(size, size), norm='ortho').reshape(-1)[mask]
+    y = y + C4_NOISE * (rng.standard_normal(m) + 1j * rng.standard_normal(m))
+    return mask, y, C4_NOISE * np.sqrt(2 * m)
+
+
+def c4_solver(size, mask, y, eps, iters, output, ctype='complex64'):
+    from pycsou_b200.func.base import ProxFuncHStack
+    from pycsou_b200.func.loss import L2BallLoss
+    from pycsou_b200.func.penalty import L21Norm, tv_groups
+    from pycsou_b200.linop.base import LinOpVStack
+    from pycsou_b200.linop.diff import Gradient
+    from pycsou_b200.linop.sampling import Masking
+    from pycsou_b200.linop.transform import DFT2
+    from pycsou_b200.opt.proxalgs import CPS
+    N = size * size
+    M = Masking(size=N, sampling_bool=mask, dtype=ctype)
+    m = M.shape[0]
+    MF = M * DFT2((size, size), dtype=ctype)
+    MF.lipschitz_cst = MF.diff_lipschitz_cst = 1.0
+    Gr = Gradient(shape=(size, size), kind='forward', dtype=ctype)
+    Gr.lipschitz_cst = Gr.diff_lipschitz_cst = float(np.sqrt(8.))
+    H = ProxFuncHStack(L2BallLoss(dim=m, data=y, radius=eps), C4_LAM * L21Norm(dim=2 * N, groups=tv_groups(N)))
+    return CPS(dim=N, G=None, H=H, K=LinOpVStack(MF, Gr), tau=1 / 3, sigma=1 / 3, rho=1, max_iter=iters - 1,
+               min_iter=iters - 1, accuracy_threshold=0, verbose=None, dtype=ctype, output=output)
+
+
+def c4_cpu_sample(size, mask, y, eps, iters):
+    """``iters`` Chambolle-Pock updates of one problem on the numpy oracle port (complex128, as the reference computes)."""
+    from oracle import np_oracle as O            # checker / CPU baseline only -- never on the product path
+    N = size * size
+    M = O.Masking(N, mask, dtype=np.complex128)
+    m = M.shape[0]
+    Ko = O.LinOpVStackOracle(O.Comp(M, O.FFT2Ortho((size, size))), O.Gradient((size, size), kind='forward', dtype='complex128'))
+    Ho = O.ProxHStack(O.PreCompShift(O.L2Ball(m, eps), y), C4_LAM * O.TVL21Norm(2 * N, N))
+    t0 = time.perf_counter()
+    O.pds_iterate(N, G=None, H=Ho, K=Ko, tau=1 / 3, sigma=1 / 3, rho=1, x0=np.zeros(N, dtype=np.complex128),
+                  z0=np.zeros(m + 2 * N, dtype=np.complex128), max_iter=iters - 1, min_iter=iters - 1,
+                  accuracy_threshold=0)
+    return time.perf_counter() - t0, 1
+
+
+def c4_arm(args, rank, local_rank, world):
+    """BASELINE.json configs[3]: independent compressed-sensing MRI problems, one subset per GPU, no data-path
+    collective.  A step = --iters Chambolle-Pock updates of every problem of the rank."""
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise RuntimeError('bench.py needs a CUDA device (no CPU fallback on the product path)')
+    torch.cuda.set_device(local_rank)
+    from pycsou_b200 import _lib
+    _lib.lib()
+    size, iters, P = args.c4_size, args.iters, args.c4_problems
+    N = size * size
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    probs = [c4_problem(size, rank * P + i) for i in range(P)]
+    m_tot = sum(int(pr[0].sum()) for pr in probs)
+    y_host = [torch.from_numpy(pr[1].astype(np.complex64)).pin_memory() for pr in probs]
+    solvers = [c4_solver(size, pr[0], yh.to('cuda'), pr[2], iters, 'torch') for pr, yh in zip(probs, y_host)]
+    for _ in range(args.warmup):
+        for s in solvers:
+            s.reset()
+            s.iterate()
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = _lib.launch_count
+    ev0.record()
+    for _ in range(args.steps):
+        for s in solvers:
+            s.reset()
+            est, _, _ = s.iterate()
+    ev1.record()
+    barrier()
+    launches = _lib.launch_count - launches0
+    dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    plan = type(solvers[0]._plan).__name__ if solvers[0]._plan is not None else 'generic (op-by-op)'
+    cs = est['primal_variable'].abs().double().sum().reshape(1)
+    checksum = float(cs.item())
+
+    # ---- end to end: host samples in, host image out, every problem of every step ----
+    e2e_solvers = [c4_solver(size, pr[0], yh, pr[2], iters, 'numpy') for pr, yh in zip(probs, y_host)]
+
+    def e2e_step():
+        out = None
+        for s, yh in zip(e2e_solvers, y_host):
+            s._plan = None                                   # a new solve of new data: the data are uploaded again
+            s._plan_key = None
+            s.reset()
+            out, _, _ = s.iterate()
+        return out
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out = e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    clocks = sampler.stop() if sampler is not None else None
+    assert out['primal_variable'].shape == (N,)
+
+    total = world * args.steps * P * iters                   # problem-iterations
+    ips = total / (dev_ms * 1e-3)
+    ms_pi = dev_ms / (args.steps * P * iters)
+    peak, peak_src = hbm_peak()
+    alg = (6 * N + 3 * m_tot / P) * 8                        # SURVEY 8(d): (6N + 3m) s per problem-iteration, FFT passes not counted
+    achieved = alg / (ms_pi * 1e-3) / 1e9
+    line = {
+        'metric': 'cps_problem_iterations_per_sec', 'value': ips, 'unit': 'iter/s', 'n_gpus': world, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': dev_ms / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'c64', 'data': 'synthetic',
+        'config': {'workload': f'compressed-sensing MRI {size}x{size} complex64, 2-D DFT + random Masking (30 %) + TV, '
+                               f'ChambollePock, {P} independent problems per GPU (BASELINE.json configs[3])',
+                   'iters_per_step': iters, 'problems_per_gpu': P, 'ms_per_problem_iteration': ms_pi,
+                   'solver_path': plan,
+                   'parallelism': f'{world * P} independent problems, {P} per GPU, no data-path collective',
+                   'l2_policy': f'working set {10 * N * 8 / 1e6:.0f} MB per problem > 126 MB L2 (no flush needed)',
+                   'effective_gbs_per_gpu': achieved, 'checksum_abs_x': checksum},
+        'e2e': {'value': total / e2e_s, 'unit': 'iter/s', 'h2d_bytes_per_step': int(m_tot * 8),
+                'd2h_bytes_per_step': int(P * (3 * N * 8) + m_tot * 8), 'ms_per_step': 1e3 * e2e_s / args.steps},
+        'gpu_launches': launches,
+        'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+                     'traffic': None, 'peak_source': peak_src, 'algorithmic_bytes': alg,
+                     'per': 'one problem-iteration: 3 kernels of this library + 2 cuFFT transforms whose passes are '
+                            'NOT counted in the algorithmic bytes (SURVEY 8(d): the fraction is structurally < 50 %)'},
+        'clocks': clocks,
+    }
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            mask, y, eps = probs[0]
+            c4_cpu_sample(size, mask, y, eps, 1)
+            dt, cores = c4_cpu_sample(size, mask, y, eps, args.cpu_iters)
+            line['cpu_baseline'] = {'value': args.cpu_iters / dt, 'unit': 'iter/s', 'cores': cores, 'kind': 'port',
+                                    'sample': f'{args.cpu_iters} Chambolle-Pock updates of one {size}x{size} complex128 '
+                                              f'problem (numpy oracle port, {_cpu_model()})'}
+        print(json.dumps(line), flush=True)
+
+
 # ------------------------------------------------------------------------------------------------ C5 (strong scaling)
 def c5_rows_on_device(Hg, W, r0, r1, psf, tdt, torch):
     """Rows [r0, r1) of the synthetic Hg x W observation, built on the device: piecewise-constant phantom, blurred by
@@ -534,6 +700,8 @@ def main():
             if args.iters == 100:
                 args.iters = 50
             c5_arm(args, rank, local_rank, world)
+        elif args.workload == 'c4':
+            c4_arm(args, rank, local_rank, world)
         else:
             b200_arm(args, rank, local_rank, world)
     finally:

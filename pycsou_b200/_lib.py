@@ -73,6 +73,14 @@ PLAIN = {
     'pcs_peer_free': ([P], I32),
     'pcs_peer_can_access': ([I32, I32], I32),
     'pcs_apgd_conv1d_run_max_n': ([], I64),
+    # fused ChambollePock iteration for compressed-sensing MRI (csrc/pcs_cps.cu); complex64 / complex128
+    'pcs_cps_mri_workspace_bytes': ([], I64),
+    'pcs_cps_mri_scatter_c64': ([P, P, P, I64, I64, P], I32),
+    'pcs_cps_mri_scatter_c128': ([P, P, P, I64, I64, P], I32),
+    'pcs_cps_mri_tv_step_c64': ([P] * 6 + [I64, I64] + [F64] * 6 + [P, P, P], I32),
+    'pcs_cps_mri_tv_step_c128': ([P] * 6 + [I64, I64] + [F64] * 6 + [P, P, P], I32),
+    'pcs_cps_mri_ball_step_c64': ([P] * 5 + [I64, F64, F64, F64, P, P, P], I32),
+    'pcs_cps_mri_ball_step_c128': ([P] * 5 + [I64, F64, F64, F64, P, P, P], I32),
     'pcs_version': ([], I32),
     'pcs_num_sms': ([], I32),
 }

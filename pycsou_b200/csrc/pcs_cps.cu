@@ -1,0 +1,291 @@
+// libpcsb200: fused Chambolle-Pock iteration for compressed-sensing MRI with a TV penalty (complex data, sm_100a).
+//
+// BASELINE.json configs[3] / SURVEY.md 8(d) "C4":  ChambollePockSplitting (= PrimalDualSplitting with F = None, rho = 1;
+// pycsou/opt/proxalgs.py:628-713, update_iterand :343-355, update_diagnostics :357-394) on
+//     K = LinOpVStack(Masking * DFT, Gradient(shape, kind='forward'))            (linop/base.py:159-314, sampling.py:125-196,
+//                                                                                 linop/diff.py:777-882)
+//     H = ProxFuncHStack(L2BallLoss(m, y, eps), lam * L21Norm(2N, TV groups))    (func/base.py:21-89, func/loss.py:69,
+//                                                                                 func/penalty.py:134-191, 480-560)
+//     G = None,  dual variable z = [u (m samples) ; w0 ; w1 (N pixels each)],  all complex.
+// One iteration is
+//     S  = Mask^T u                 (pcs_cps_mri_scatter: zero fill + scatter)           [cuFFT: g = DFT^H S]
+//     xt = x - tau (g + Grad^T w),  v = 2 xt - x,  x' = rho xt + (1-rho) x
+//     w' = rho fenchel_prox_{sigma lam L21}(w + sigma Grad v) + (1-rho) w                 (pcs_cps_mri_tv_step: one kernel,
+//                                                                                          v through shared memory)
+//                                                                                         [cuFFT: V = DFT v]
+//     p  = u + sigma V[mask],  u' = rho (p - sigma (y + proj_ball_eps(p/sigma - y))) + (1-rho) u   (pcs_cps_mri_ball_step:
+//                                                                                          norm pass + update pass over m)
+// and the four sums ||x'-x||^2, ||x||^2, ||z'-z||^2, ||z||^2 of update_diagnostics (deterministic reductions).
+// The two DFTs are library calls made by the host (cuFFT through torch.fft), exactly where the reference calls pocketfft.
+// HBM traffic per iteration outside the FFTs: read x, g, w (4 N), write x', w', v (4 N), S (N + m) and 6 m for the ball step.
+#include "pcs_common.cuh"
+#include <math.h>
+
+using namespace pcs;
+
+namespace {
+
+template <typename R> struct Cx;
+template <> struct Cx<float> { typedef float2 type; };
+template <> struct Cx<double> { typedef double2 type; };
+
+template <typename V, typename R> __device__ __forceinline__ V cmake(R a, R b) { V v; v.x = a; v.y = b; return v; }
+template <typename V> __device__ __forceinline__ V cadd(V a, V b) { a.x += b.x; a.y += b.y; return a; }
+template <typename V> __device__ __forceinline__ V csub(V a, V b) { a.x -= b.x; a.y -= b.y; return a; }
+template <typename V, typename R> __device__ __forceinline__ V cscale(V a, R s) { a.x *= s; a.y *= s; return a; }
+// a + s b
+template <typename V, typename R> __device__ __forceinline__ V caxpy(V a, R s, V b) {
+    a.x = fma(s, b.x, a.x); a.y = fma(s, b.y, a.y); return a;
+}
+template <typename V> __device__ __forceinline__ double cabs2(V a) { return (double)a.x * a.x + (double)a.y * a.y; }
+
+template <typename R> __device__ __forceinline__ R rsq(R v);
+template <> __device__ __forceinline__ float rsq<float>(float v) { return rsqrtf(v); }
+template <> __device__ __forceinline__ double rsq<double>(double v) { return rsqrt(v); }
+template <typename R> __device__ __forceinline__ R tiny();
+template <> __device__ __forceinline__ float tiny<float>() { return 1e-30f; }
+template <> __device__ __forceinline__ double tiny<double>() { return 1e-300; }
+
+constexpr int CPS_TH = 32;                 // tile rows
+constexpr int CPS_NT = 256;
+constexpr int CPS_MAX_BLOCKS = 4096;       // partial-sum slots in the workspace
+template <typename R> struct TileW { static constexpr int value = sizeof(R) == 4 ? 128 : 64; };   // tile columns
+
+template <typename R> struct CpsTvArgs {
+    typedef typename Cx<R>::type V;
+    V* x_out; V* w_out; V* v_out;
+    const V* x; const V* w; const V* g;
+    int H, W;
+    R lam, tau, sigma, rho, omr, is0, is1;
+    double* partials; unsigned int* ticket; double* diag_out;
+};
+
+template <typename R>
+__global__ void __launch_bounds__(CPS_NT) cps_tv_kernel(const CpsTvArgs<R> A) {
+    typedef typename Cx<R>::type V;
+    constexpr int TH = CPS_TH, TW = TileW<R>::value, PW = TW + 1;
+    extern __shared__ __align__(16) unsigned char smem[];
+    V* const sv = reinterpret_cast<V*>(smem);                                   // v on the (TH+1) x (TW+1) points of the tile
+    double* const red = reinterpret_cast<double*>(smem + (size_t)(TH + 1) * PW * sizeof(V));
+    const int tid = threadIdx.x, H = A.H, W = A.W;
+    const int tiles_w = (W + TW - 1) / TW, tiles_h = (H + TH - 1) / TH;
+    const int64_t N = (int64_t)H * W;
+    const V* __restrict__ w0 = A.w;
+    const V* __restrict__ w1 = A.w + N;
+    double s_dx = 0.0, s_x = 0.0, s_dw = 0.0, s_w = 0.0;
+    const V zero = cmake<V, R>(R(0), R(0));
+
+    for (int tile = blockIdx.x; tile < tiles_w * tiles_h; tile += gridDim.x) {
+        const int ti = tile / tiles_w, tj = tile - ti * tiles_w;
+        const int i0 = ti * TH, j0 = tj * TW;
+        // primal update on the tile plus one row below / one column to the right (the forward differences of v need them)
+        for (int p = tid; p < (TH + 1) * PW; p += CPS_NT) {
+            const int r = p / PW, c = p - r * PW;
+            const int gi = i0 + r, gj = j0 + c;
+            V v = zero;
+            if (gi < H && gj < W) {
+                const int64_t idx = (int64_t)gi * W + gj;
+                const V x = A.x[idx], g = A.g[idx];
+                // Gradient^T w (pylops FirstDerivative forward, adjoint: y[:-1] -= z[:-1]/h; y[1:] += z[:-1]/h)
+                const V w0c = gi < H - 1 ? w0[idx] : zero, w0u = gi > 0 ? w0[idx - W] : zero;
+                const V w1c = gj < W - 1 ? w1[idx] : zero, w1l = gj > 0 ? w1[idx - 1] : zero;
+                V a = cscale(csub(w0u, w0c), A.is0);
+                a = caxpy(a, A.is1, csub(w1l, w1c));
+                const V xt = caxpy(x, -A.tau, cadd(g, a));
+                v = caxpy(cscale(x, R(-1)), R(2), xt);
+                if (r < TH && c < TW) {
+                    const V xn = caxpy(cscale(x, A.omr), A.rho, xt);
+                    A.x_out[idx] = xn;
+                    A.v_out[idx] = v;
+                    s_dx += cabs2(csub(xn, x));
+                    s_x += cabs2(x);
+                }
+            }
+            sv[p] = v;
+        }
+        __syncthreads();
+        // dual update of the TV block: w' = rho P_{lam-ball}(w + sigma Grad v) + (1 - rho) w
+        // (fenchel_prox of lam * L21Norm, core/functional.py:207 + func/penalty.py:551-557, in its projection form)
+        for (int p = tid; p < TH * TW; p += CPS_NT) {
+            const int r = p / TW, c = p - r * TW;
+            const int gi = i0 + r, gj = j0 + c;
+            if (gi < H && gj < W) {
+                const int64_t idx = (int64_t)gi * W + gj;
+                const V vc = sv[r * PW + c], vd = sv[(r + 1) * PW + c], vr = sv[r * PW + c + 1];
+                const V d0 = gi < H - 1 ? cscale(csub(vd, vc), A.is0) : zero;
+                const V d1 = gj < W - 1 ? cscale(csub(vr, vc), A.is1) : zero;
+                const V a0 = w0[idx], a1 = w1[idx];
+                const V q0 = caxpy(a0, A.sigma, d0), q1 = caxpy(a1, A.sigma, d1);
+                const R ss = fma(q0.x, q0.x, fma(q0.y, q0.y, fma(q1.x, q1.x, fma(q1.y, q1.y, tiny<R>()))));
+                R f = A.lam * rsq<R>(ss);
+                f = f < R(1) ? f : R(1);
+                const V n0 = caxpy(cscale(a0, A.omr), A.rho * f, q0), n1 = caxpy(cscale(a1, A.omr), A.rho * f, q1);
+                A.w_out[idx] = n0;
+                A.w_out[N + idx] = n1;
+                s_dw += cabs2(csub(n0, a0)) + cabs2(csub(n1, a1));
+                s_w += cabs2(a0) + cabs2(a1);
+            }
+        }
+        __syncthreads();
+    }
+    double v4[4] = {s_dx, s_x, s_dw, s_w};
+    grid_sum_finish<4, CPS_NT>(v4, A.partials, A.ticket, A.diag_out, red);
+}
+
+template <typename R>
+__global__ void __launch_bounds__(CPS_NT) cps_scatter_kernel(typename Cx<R>::type* __restrict__ out,
+                                                             const typename Cx<R>::type* __restrict__ u,
+                                                             const int64_t* __restrict__ idx, int64_t m) {
+    for (int64_t k = blockIdx.x * (int64_t)CPS_NT + threadIdx.x; k < m; k += (int64_t)gridDim.x * CPS_NT) out[idx[k]] = u[k];
+}
+
+template <typename R> struct CpsBallArgs {
+    typedef typename Cx<R>::type V;
+    V* u_out; const V* u; const V* spec; const int64_t* idx; const V* y;
+    int64_t m;
+    R eps, sigma, inv_sigma, rho, omr;
+    double* partials; unsigned int* ticket; double* sumsq; double* tmp; double* diag;
+};
+
+// d = (u + sigma V[mask]) / sigma - y for sample k (fenchel_prox evaluates prox at z / sigma, core/functional.py:207;
+// the loss shifts by -y, func/loss.py:69)
+template <typename R>
+__device__ __forceinline__ void ball_point(const CpsBallArgs<R>& A, int64_t k, typename Cx<R>::type& p,
+                                           typename Cx<R>::type& d) {
+    p = caxpy(A.u[k], A.sigma, A.spec[A.idx[k]]);
+    d = csub(cscale(p, A.inv_sigma), A.y[k]);
+}
+
+template <typename R> __global__ void __launch_bounds__(CPS_NT) cps_ball_norm_kernel(const CpsBallArgs<R> A) {
+    typedef typename Cx<R>::type V;
+    __shared__ double red[CPS_NT / 32];
+    double acc = 0.0;
+    for (int64_t k = blockIdx.x * (int64_t)CPS_NT + threadIdx.x; k < A.m; k += (int64_t)gridDim.x * CPS_NT) {
+        V p, d;
+        ball_point<R>(A, k, p, d);
+        acc += cabs2(d);
+    }
+    double v1[1] = {acc};
+    grid_sum_finish<1, CPS_NT>(v1, A.partials, A.ticket, A.sumsq, red);
+}
+
+// proj_l2_ball (math/prox.py:207-210): x if ||x|| <= r else r x / ||x||; then the Moreau identity and the momentum step
+template <typename R> __global__ void __launch_bounds__(CPS_NT) cps_ball_apply_kernel(const CpsBallArgs<R> A) {
+    typedef typename Cx<R>::type V;
+    __shared__ double red[2 * (CPS_NT / 32)];
+    const double nrm = sqrt(*A.sumsq);
+    const bool inside = nrm <= (double)A.eps;
+    const R f = inside ? R(1) : (R)((double)A.eps / nrm);
+    double s_du = 0.0, s_u = 0.0;
+    for (int64_t k = blockIdx.x * (int64_t)CPS_NT + threadIdx.x; k < A.m; k += (int64_t)gridDim.x * CPS_NT) {
+        V p, d;
+        ball_point<R>(A, k, p, d);
+        const V prox = cadd(inside ? d : cscale(d, f), A.y[k]);
+        const V ut = caxpy(p, -A.sigma, prox);
+        const V uo = A.u[k];
+        const V un = caxpy(cscale(uo, A.omr), A.rho, ut);
+        A.u_out[k] = un;
+        s_du += cabs2(csub(un, uo));
+        s_u += cabs2(uo);
+    }
+    double v2[2] = {s_du, s_u};
+    const bool last = grid_sum_finish<2, CPS_NT>(v2, A.partials, A.ticket, A.tmp, red);
+    if (last && threadIdx.x == 0) {          // the TV kernel of this iteration wrote the w part of the dual sums
+        A.diag[2] += A.tmp[0];
+        A.diag[3] += A.tmp[1];
+    }
+}
+
+// workspace (doubles): [0, 4 MAXB) partial sums | ticket | tmp[4] | sumsq
+constexpr size_t CPS_WS_DOUBLES = 4 * (size_t)CPS_MAX_BLOCKS + 8;
+
+template <typename R>
+int cps_scatter_impl(void* spec_out, const void* u, const void* idx, int64_t N, int64_t m, cudaStream_t s) {
+    typedef typename Cx<R>::type V;
+    const char* what = "pcs_cps_mri_scatter";
+    PCS_REQUIRE(N >= 1 && m >= 0 && m <= N, "%s: bad sizes", what);
+    PCS_REQUIRE(spec_out && (m == 0 || (u && idx)), "%s: null pointer", what);
+    if (cudaMemsetAsync(spec_out, 0, (size_t)N * sizeof(V), s) != cudaSuccess) return check_launch(what);
+    if (m > 0) {
+        const int64_t nb = (m + CPS_NT - 1) / CPS_NT;
+        const int grid = (int)(nb < 8 * (int64_t)num_sms() ? nb : 8 * (int64_t)num_sms());
+        cps_scatter_kernel<R><<<grid, CPS_NT, 0, s>>>((V*)spec_out, (const V*)u, (const int64_t*)idx, m);
+    }
+    return check_launch(what);
+}
+
+template <typename R>
+int cps_tv_impl(void* x_out, void* w_out, void* v_out, const void* x, const void* w, const void* g, int64_t H, int64_t W,
+                double lam, double tau, double sigma, double rho, double step0, double step1, double* diag_out,
+                void* workspace, cudaStream_t s) {
+    typedef typename Cx<R>::type V;
+    const char* what = "pcs_cps_mri_tv_step";
+    PCS_REQUIRE(H >= 1 && W >= 1 && H < (1ll << 30) && W < (1ll << 30), "%s: bad dimensions", what);
+    PCS_REQUIRE(x_out && w_out && v_out && x && w && g && diag_out && workspace, "%s: null pointer", what);
+    PCS_REQUIRE(x_out != x && w_out != w, "%s: outputs must not alias inputs (ping-pong)", what);
+    PCS_REQUIRE(lam > 0 && tau > 0 && sigma > 0 && step0 != 0 && step1 != 0, "%s: tau, sigma, lam must be positive", what);
+    CpsTvArgs<R> A;
+    A.x_out = (V*)x_out; A.w_out = (V*)w_out; A.v_out = (V*)v_out;
+    A.x = (const V*)x; A.w = (const V*)w; A.g = (const V*)g;
+    A.H = (int)H; A.W = (int)W;
+    A.lam = (R)lam; A.tau = (R)tau; A.sigma = (R)sigma; A.rho = (R)rho; A.omr = (R)(1 - rho);
+    A.is0 = (R)(1 / step0); A.is1 = (R)(1 / step1);
+    A.partials = (double*)workspace;
+    A.ticket = (unsigned int*)((double*)workspace + 4 * (size_t)CPS_MAX_BLOCKS);
+    A.diag_out = diag_out;
+    constexpr int TW = TileW<R>::value;
+    const int64_t ntiles = ((H + CPS_TH - 1) / CPS_TH) * ((W + TW - 1) / TW);
+    const int64_t cap = 4 * (int64_t)num_sms() < CPS_MAX_BLOCKS ? 4 * (int64_t)num_sms() : CPS_MAX_BLOCKS;
+    const int grid = (int)(ntiles < cap ? ntiles : cap);
+    const size_t smem = (size_t)(CPS_TH + 1) * (TW + 1) * sizeof(V) + 4 * (CPS_NT / 32) * sizeof(double);
+    cps_tv_kernel<R><<<grid, CPS_NT, smem, s>>>(A);
+    return check_launch(what);
+}
+
+template <typename R>
+int cps_ball_impl(void* u_out, const void* u, const void* spec, const void* idx, const void* y, int64_t m, double eps,
+                  double sigma, double rho, double* diag_inout, void* workspace, cudaStream_t s) {
+    typedef typename Cx<R>::type V;
+    const char* what = "pcs_cps_mri_ball_step";
+    PCS_REQUIRE(m >= 0 && sigma > 0 && eps >= 0, "%s: bad arguments", what);
+    PCS_REQUIRE(diag_inout && workspace && (m == 0 || (u_out && u && spec && idx && y)), "%s: null pointer", what);
+    if (m == 0) return 0;
+    CpsBallArgs<R> A;
+    A.u_out = (V*)u_out; A.u = (const V*)u; A.spec = (const V*)spec; A.idx = (const int64_t*)idx; A.y = (const V*)y;
+    A.m = m;
+    A.eps = (R)eps; A.sigma = (R)sigma; A.inv_sigma = (R)(1 / sigma); A.rho = (R)rho; A.omr = (R)(1 - rho);
+    double* ws = (double*)workspace;
+    A.partials = ws;
+    A.ticket = (unsigned int*)(ws + 4 * (size_t)CPS_MAX_BLOCKS);
+    A.tmp = ws + 4 * (size_t)CPS_MAX_BLOCKS + 1;
+    A.sumsq = ws + 4 * (size_t)CPS_MAX_BLOCKS + 5;
+    A.diag = diag_inout;
+    const int64_t nb = (m + CPS_NT - 1) / CPS_NT;
+    const int64_t cap = 8 * (int64_t)num_sms() < CPS_MAX_BLOCKS ? 8 * (int64_t)num_sms() : CPS_MAX_BLOCKS;
+    const int grid = (int)(nb < cap ? nb : cap);
+    cps_ball_norm_kernel<R><<<grid, CPS_NT, 0, s>>>(A);
+    cps_ball_apply_kernel<R><<<grid, CPS_NT, 0, s>>>(A);
+    return check_launch(what);
+}
+
+}  // namespace
+
+extern "C" int64_t pcs_cps_mri_workspace_bytes(void) { return (int64_t)(CPS_WS_DOUBLES * sizeof(double)); }
+
+#define PCS_EXPORT_CPLX(name, impl, params, args)                          \
+    extern "C" int name##_c64 params { return impl<float> args; }          \
+    extern "C" int name##_c128 params { return impl<double> args; }
+
+PCS_EXPORT_CPLX(pcs_cps_mri_scatter, cps_scatter_impl,
+                (void* spec_out, const void* u, const void* idx_i64, int64_t N, int64_t m, void* stream),
+                (spec_out, u, idx_i64, N, m, (cudaStream_t)stream))
+PCS_EXPORT_CPLX(pcs_cps_mri_tv_step, cps_tv_impl,
+                (void* x_out, void* w_out, void* v_out, const void* x, const void* w, const void* g, int64_t H, int64_t W,
+                 double lam, double tau, double sigma, double rho, double step0, double step1, void* diag_out_f64,
+                 void* workspace, void* stream),
+                (x_out, w_out, v_out, x, w, g, H, W, lam, tau, sigma, rho, step0, step1, (double*)diag_out_f64, workspace,
+                 (cudaStream_t)stream))
+PCS_EXPORT_CPLX(pcs_cps_mri_ball_step, cps_ball_impl,
+                (void* u_out, const void* u, const void* spec, const void* idx_i64, const void* y, int64_t m, double eps,
+                 double sigma, double rho, void* diag_inout_f64, void* workspace, void* stream),
+                (u_out, u, spec, idx_i64, y, m, eps, sigma, rho, (double*)diag_inout_f64, workspace, (cudaStream_t)stream))

@@ -239,8 +239,107 @@ def K_device():
     return device()
 
 
+class CpsMriPlan:
+    """Compressed-sensing MRI with a TV penalty (BASELINE.json configs[3]) on the kernels of ``csrc/pcs_cps.cu``.
+
+    ``K = LinOpVStack(Masking * DFT2, Gradient(forward))``, ``H = ProxFuncHStack(L2BallLoss(m, y, eps), lam * L21Norm)``,
+    ``F = G = None``, complex iterates; dual variable ``z = [u (m) ; w0 ; w1]``.  One update = three launches of this
+    library (scatter, fused primal + TV-dual stencil, data-consistency ball) and the two DFTs (cuFFT through
+    ``torch.fft``, where the reference calls pocketfft), instead of ~25 stand-alone kernels.
+    """
+
+    def __init__(self, solver, H, W, steps, mask_op, dft, y, eps, lam):
+        self.solver = solver
+        self.H, self.W, self.steps = H, W, steps
+        self.N, self.m = H * W, int(mask_op.nb_of_samples)
+        dt = solver._dtype
+        self.dtype = dt
+        self.sfx = '_c64' if dt == torch.complex64 else '_c128'
+        dev = K_device()
+        self.idx = mask_op._idx(dev)
+        self.dft = dft
+        self.y = to_device(y, dt)
+        if self.y.numel() != self.m:
+            raise _NoMatch('data size mismatch')
+        self.eps, self.lam = float(eps), float(lam)
+        self.ws = torch.zeros(int(_lib.call_plain('pcs_cps_mri_workspace_bytes')) // 8, dtype=torch.float64, device=dev)
+        self.spec = torch.empty(self.N, dtype=dt, device=dev)      # Mask^T u, then DFT v
+        self.g = torch.empty(self.N, dtype=dt, device=dev)         # DFT^H Mask^T u
+        self.v = torch.empty(self.N, dtype=dt, device=dev)         # 2 xt - x
+        self._xbuf, self._zbuf = [None, None], [None, None]
+
+    _out = PdsTvPlan._out
+    release = PdsTvPlan.release
+
+    def step(self, x, z, drow):
+        s = self.solver
+        m, N, shp = self.m, self.N, (self.H, self.W)
+        tau, sigma, rho = float(s.tau), float(s.sigma), float(s.rho)
+        xo, zo = self._out(self._xbuf, x), self._out(self._zbuf, z)
+        st = K.stream()
+        _lib.call('pcs_cps_mri_scatter' + self.sfx, self.spec.data_ptr(), z.data_ptr(), self.idx.data_ptr(), N, m, st)
+        torch.fft.ifft2(self.spec.view(shp), norm='ortho', out=self.g.view(shp))
+        _lib.call('pcs_cps_mri_tv_step' + self.sfx, xo.data_ptr(), zo[m:].data_ptr(), self.v.data_ptr(), x.data_ptr(),
+                  z[m:].data_ptr(), self.g.data_ptr(), self.H, self.W, self.lam, tau, sigma, rho, self.steps[0],
+                  self.steps[1], drow.data_ptr(), self.ws.data_ptr(), st)
+        torch.fft.fft2(self.v.view(shp), norm='ortho', out=self.spec.view(shp))
+        _lib.call('pcs_cps_mri_ball_step' + self.sfx, zo.data_ptr(), z.data_ptr(), self.spec.data_ptr(),
+                  self.idx.data_ptr(), self.y.data_ptr(), m, self.eps, sigma, rho, drow.data_ptr(), self.ws.data_ptr(), st)
+        return xo, zo
+
+
+def plan_cps_mri(solver):
+    """Fused plan for the compressed-sensing MRI problem shape (complex iterates), or None."""
+    from ..core.functional import ProxFuncPreComp
+    from ..core.linop import LinOpComp
+    from ..func.base import IndicatorFunctional, NullDifferentiableFunctional, NullProximableFunctional, ProxFuncHStack
+    from ..func.penalty import L21Norm
+    from ..linop.base import LinOpStack
+    from ..linop.diff import GradientOperator
+    from ..linop.sampling import Masking
+    from ..linop.transform import DFT2
+    from .._array import Negated
+    try:
+        if not (isinstance(solver.F, NullDifferentiableFunctional) and isinstance(solver.G, NullProximableFunctional)):
+            raise _NoMatch('F and G must be None')
+        Kop, Hf = solver.K, solver.H
+        if not (isinstance(Kop, LinOpStack) and Kop.axis == 0 and len(Kop.linops) == 2):
+            raise _NoMatch('K is not a vertical stack of two operators')
+        MF, Gr = Kop.linops
+        if not (isinstance(MF, LinOpComp) and isinstance(MF.LinOp1, Masking) and isinstance(MF.LinOp2, DFT2)
+                and MF.LinOp2.batch == 1):
+            raise _NoMatch('first block is not Masking * DFT2')
+        if not (isinstance(Gr, GradientOperator) and Gr.kind == 'forward' and len(Gr.array_shape) == 2
+                and tuple(Gr.array_shape) == tuple(MF.LinOp2.array_shape)):
+            raise _NoMatch('second block is not a forward-difference Gradient on the DFT grid')
+        H, W = Gr.array_shape
+        N = H * W
+        if N != solver.dim or H < 2 or W < 2 or MF.LinOp1.input_size != N:
+            raise _NoMatch('shape mismatch')
+        if not (isinstance(Hf, ProxFuncHStack) and len(Hf.proxfuncs) == 2):
+            raise _NoMatch('H is not a stack of two functionals')
+        ball, tv = Hf.proxfuncs
+        if not (isinstance(ball, ProxFuncPreComp) and ball.scale == 1 and isinstance(ball.prox_func, IndicatorFunctional)
+                and ball.prox_func.kind == 'l2ball' and ball.dim == MF.LinOp1.nb_of_samples):
+            raise _NoMatch('first functional is not an L2BallLoss on the samples')
+        sh = ball.shift
+        if isinstance(sh, Number):
+            raise _NoMatch('scalar data')
+        y = sh.a if isinstance(sh, Negated) else (-sh if isinstance(sh, torch.Tensor) else -np.asarray(sh))
+        f, lam = _scaled(tv)
+        if not (type(f) is L21Norm and f._is_planes and f.n_comp == 2 and f.n_groups == N):
+            raise _NoMatch('second functional is not a TV penalty')
+        if not (float(solver.tau) > 0 and float(solver.sigma) > 0 and lam > 0):
+            raise _NoMatch('non-positive step')
+        return CpsMriPlan(solver, H, W, Gr.steps, MF.LinOp1, MF.LinOp2, y, ball.prox_func.params[0], lam)
+    except _NoMatch:
+        return None
+
+
 def plan_pds(solver):
     """Fused plan for a ``PrimalDualSplitting`` instance, or None (generic op-by-op path)."""
+    if solver._H and solver._dtype in (torch.complex64, torch.complex128):
+        return plan_cps_mri(solver)
     if not solver._H or solver._dtype not in (torch.float32, torch.float64):
         return None
     try:

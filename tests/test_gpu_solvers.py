@@ -217,7 +217,7 @@ def test_iterates_generator_and_torch_output():
     assert isinstance(est3['primal_variable'], torch.Tensor) and est3['primal_variable'].is_cuda
 
 
-def _c4_solver(shape, mask, y, lam, eps, k, dtype='complex128', output='numpy'):
+def _c4_solver(shape, mask, y, lam, eps, k, dtype='complex128', output='numpy', fused=True):
     """BASELINE.json configs[3] exactly as tests/golden/gen_golden.py:c4_csmri builds it with the reference classes."""
     from pycsou_b200.func.base import ProxFuncHStack
     from pycsou_b200.func.loss import L2BallLoss
@@ -235,7 +235,7 @@ def _c4_solver(shape, mask, y, lam, eps, k, dtype='complex128', output='numpy'):
     H = ProxFuncHStack(L2BallLoss(dim=m, data=y, radius=eps), lam * L21Norm(2 * N, np.tile(np.arange(N), 2)))
     return CPS(dim=N, G=None, H=H, K=Kop, tau=1 / 3, sigma=1 / 3, rho=1, x0=np.zeros(N, dtype=dtype),
                z0=np.zeros(m + 2 * N, dtype=dtype), max_iter=k - 1, min_iter=k - 1, accuracy_threshold=0,
-               verbose=None, output=output), m
+               verbose=None, output=output, fused=fused), m
 
 
 def test_c4_csmri_cps_complex128():
@@ -247,6 +247,7 @@ def test_c4_csmri_cps_complex128():
         s, m = _c4_solver(shape, mask, y, meta['lam'], meta['eps'], k)
         assert m == meta['m']                                   # sampling mask bit-exact: same sample count and order
         est, _, _ = s.iterate()
+        assert type(s._plan).__name__ == 'CpsMriPlan'           # the fused kernels of csrc/pcs_cps.cu ran
         assert np.iscomplexobj(est['primal_variable'])
         assert rel_l2(est['primal_variable'], g[f'x_k{k}']) < TOL64
         assert rel_l2(est['dual_variable'], g[f'z_k{k}']) < TOL64
@@ -267,3 +268,66 @@ def test_c4_csmri_cps_complex64_vs_oracle():
     xo, zo, _, _ = C.c4(k, mask, y, shape=shape, lam=lam, eps=eps)
     assert est['primal_variable'].dtype == np.complex64
     assert rel_l2(est['primal_variable'], xo) < 2e-4 and rel_l2(est['dual_variable'], zo) < 2e-4
+
+
+@pytest.mark.parametrize('dtype,tol', [('complex128', 1e-12), ('complex64', 2e-5)])
+@pytest.mark.parametrize('shape', [(70, 200), (33, 129), (2, 2), (64, 64)])
+def test_c4_fused_matches_op_by_op(shape, dtype, tol):
+    """Fused CPS-MRI iteration (csrc/pcs_cps.cu) against the op-by-op path (itself pinned by the golden fixture):
+    ragged tiles, tiny images, a data ball that is active (small eps) and one that is not (huge eps)."""
+    N = shape[0] * shape[1]
+    rng = np.random.default_rng(5)
+    truth = synth.phantom(shape).reshape(-1) * np.exp(1j * 2 * np.pi * (np.arange(N) / N))
+    mask = rng.random(N) < 0.35
+    mask[0] = True
+    m = int(mask.sum())
+    y = (np.fft.fft2(truth.reshape(shape), norm='ortho').reshape(-1)[mask]
+         + 0.01 * (rng.standard_normal(m) + 1j * rng.standard_normal(m))).astype(dtype)
+    for eps in (0.01 * np.sqrt(2 * m), 1e6):
+        for k in (1, 6):
+            sf, _ = _c4_solver(shape, mask, y, 0.05, eps, k, dtype=dtype)
+            ef, _, df = sf.iterate()
+            assert type(sf._plan).__name__ == 'CpsMriPlan'
+            sg, _ = _c4_solver(shape, mask, y, 0.05, eps, k, dtype=dtype, fused=False)
+            eg, _, dg = sg.iterate()
+            assert sg._plan is None
+            assert rel_l2(ef['primal_variable'], eg['primal_variable']) < tol
+            assert rel_l2(ef['dual_variable'], eg['dual_variable']) < tol
+            for col in df.columns[1:]:
+                assert np.allclose(np.asarray(df[col], float), np.asarray(dg[col], float), rtol=1e-6 if dtype == 'complex128' else 1e-3)
+
+
+def test_c4_fused_with_momentum_and_steps():
+    """rho != 1 and non-unit sampling steps through PrimalDualSplitting directly."""
+    from pycsou_b200.func.base import ProxFuncHStack
+    from pycsou_b200.func.loss import L2BallLoss
+    from pycsou_b200.func.penalty import L21Norm
+    from pycsou_b200.linop.base import LinOpVStack
+    from pycsou_b200.linop.diff import Gradient
+    from pycsou_b200.linop.sampling import Masking
+    from pycsou_b200.linop.transform import DFT2
+    from pycsou_b200.opt.proxalgs import PDS
+    shape, dtype = (40, 72), 'complex128'
+    N = shape[0] * shape[1]
+    rng = np.random.default_rng(8)
+    mask = rng.random(N) < 0.4
+    m = int(mask.sum())
+    y = rng.standard_normal(m) + 1j * rng.standard_normal(m)
+    x0 = rng.standard_normal(N) + 1j * rng.standard_normal(N)
+    z0 = rng.standard_normal(m + 2 * N) + 1j * rng.standard_normal(m + 2 * N)
+    out = {}
+    for fused in (True, False):
+        M = Masking(size=N, sampling_bool=mask, dtype=dtype)
+        MF = M * DFT2(shape, dtype=dtype)
+        MF.lipschitz_cst = MF.diff_lipschitz_cst = 1.0
+        Gr = Gradient(shape=shape, kind='forward', step=(0.5, 2.0), dtype=dtype)
+        Gr.lipschitz_cst = Gr.diff_lipschitz_cst = SQRT8 / 0.5
+        Kop = LinOpVStack(MF, Gr)
+        H = ProxFuncHStack(L2BallLoss(dim=m, data=y, radius=3.0), 0.2 * L21Norm(2 * N, np.tile(np.arange(N), 2)))
+        s = PDS(dim=N, F=None, G=None, H=H, K=Kop, tau=0.1, sigma=0.2, rho=0.8, x0=x0, z0=z0, max_iter=4, min_iter=4,
+                accuracy_threshold=0, verbose=None, fused=fused)
+        est, _, _ = s.iterate()
+        assert (type(s._plan).__name__ == 'CpsMriPlan') == fused
+        out[fused] = est
+    assert rel_l2(out[True]['primal_variable'], out[False]['primal_variable']) < 1e-12
+    assert rel_l2(out[True]['dual_variable'], out[False]['dual_variable']) < 1e-12
