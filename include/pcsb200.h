@@ -140,27 +140,31 @@ PCS_DECL_REAL(pcs_pds_tv_step,
  *   _c64: complex64 (interleaved float pairs), _c128: complex128.  Dual variable z = [u (m) ; w0 (N) ; w1 (N)].
  *   One iteration = scatter -> [host: g = DFT^H spec] -> tv_step -> [host: V = DFT v] -> ball_step:
  *     scatter:   spec_out (N) = 0; spec_out[idx] = u                                       (Masking.adjoint)
- *     tv_step:   xt = x - tau (g + Grad^T w); v = 2 xt - x; x' = rho xt + (1-rho) x;
+ *     tv_step:   xt = x - tau (gscale g + Grad^T w); v = 2 xt - x; x' = rho xt + (1-rho) x;
  *                w' = rho fenchel_prox_{sigma lam L21}(w + sigma Grad v) + (1-rho) w;
  *                diag_out[4] = ||x'-x||^2, ||x||^2, ||w'-w||^2, ||w||^2
- *     ball_step: p = u + sigma V[idx]; u' = rho (p - sigma (y + proj_{||.|| <= eps}(p/sigma - y))) + (1-rho) u;
- *                diag_inout[2] += ||u'-u||^2, diag_inout[3] += ||u||^2
- *   workspace: pcs_cps_mri_workspace_bytes() bytes, zero-initialised once, shared by the three calls of a stream. */
+ *     ball_step: p = u + sigma vscale V[idx]; u' = rho (p - sigma (y + proj_{||.|| <= eps}(p/sigma - y))) + (1-rho) u;
+ *                diag_inout[2] += ||u'-u||^2, diag_inout[3] += ||u||^2;  if spec_next != NULL also
+ *                spec_next[idx] = u' (a buffer that a scatter has filled before keeps Mask^T u' up to date: the next
+ *                iteration needs no scatter)
+ *   gscale / vscale: normalisation of the DFTs (1/sqrt(N) each when the host runs unnormalised cuFFT transforms, 1
+ *   for orthonormal ones).  workspace: pcs_cps_mri_workspace_bytes() bytes, zero-initialised once, shared by the
+ *   three calls of a stream. */
 int64_t pcs_cps_mri_workspace_bytes(void);
 int pcs_cps_mri_scatter_c64(void* spec_out, const void* u, const void* idx_i64, int64_t N, int64_t m, void* stream);
 int pcs_cps_mri_scatter_c128(void* spec_out, const void* u, const void* idx_i64, int64_t N, int64_t m, void* stream);
 int pcs_cps_mri_tv_step_c64(void* x_out, void* w_out, void* v_out, const void* x, const void* w, const void* g,
-                            int64_t H, int64_t W, double lam, double tau, double sigma, double rho, double step0,
-                            double step1, void* diag_out_f64, void* workspace, void* stream);
+                            int64_t H, int64_t W, double gscale, double lam, double tau, double sigma, double rho,
+                            double step0, double step1, void* diag_out_f64, void* workspace, void* stream);
 int pcs_cps_mri_tv_step_c128(void* x_out, void* w_out, void* v_out, const void* x, const void* w, const void* g,
-                             int64_t H, int64_t W, double lam, double tau, double sigma, double rho, double step0,
-                             double step1, void* diag_out_f64, void* workspace, void* stream);
-int pcs_cps_mri_ball_step_c64(void* u_out, const void* u, const void* spec, const void* idx_i64, const void* y,
-                              int64_t m, double eps, double sigma, double rho, void* diag_inout_f64, void* workspace,
-                              void* stream);
-int pcs_cps_mri_ball_step_c128(void* u_out, const void* u, const void* spec, const void* idx_i64, const void* y,
-                               int64_t m, double eps, double sigma, double rho, void* diag_inout_f64, void* workspace,
-                               void* stream);
+                             int64_t H, int64_t W, double gscale, double lam, double tau, double sigma, double rho,
+                             double step0, double step1, void* diag_out_f64, void* workspace, void* stream);
+int pcs_cps_mri_ball_step_c64(void* u_out, void* spec_next, const void* u, const void* spec, const void* idx_i64,
+                              const void* y, int64_t m, double vscale, double eps, double sigma, double rho,
+                              void* diag_inout_f64, void* workspace, void* stream);
+int pcs_cps_mri_ball_step_c128(void* u_out, void* spec_next, const void* u, const void* spec, const void* idx_i64,
+                               const void* y, int64_t m, double vscale, double eps, double sigma, double rho,
+                               void* diag_inout_f64, void* workspace, void* stream);
 
 /* ---- a whole AcceleratedProximalGradientDescent solve in one launch: the loop of core/solver.py:55-76 with
  *      update_iterand / update_diagnostics / stopping_metric of opt/proxalgs.py:586-622, for

@@ -77,10 +77,10 @@ PLAIN = {
     'pcs_cps_mri_workspace_bytes': ([], I64),
     'pcs_cps_mri_scatter_c64': ([P, P, P, I64, I64, P], I32),
     'pcs_cps_mri_scatter_c128': ([P, P, P, I64, I64, P], I32),
-    'pcs_cps_mri_tv_step_c64': ([P] * 6 + [I64, I64] + [F64] * 6 + [P, P, P], I32),
-    'pcs_cps_mri_tv_step_c128': ([P] * 6 + [I64, I64] + [F64] * 6 + [P, P, P], I32),
-    'pcs_cps_mri_ball_step_c64': ([P] * 5 + [I64, F64, F64, F64, P, P, P], I32),
-    'pcs_cps_mri_ball_step_c128': ([P] * 5 + [I64, F64, F64, F64, P, P, P], I32),
+    'pcs_cps_mri_tv_step_c64': ([P] * 6 + [I64, I64] + [F64] * 7 + [P, P, P], I32),
+    'pcs_cps_mri_tv_step_c128': ([P] * 6 + [I64, I64] + [F64] * 7 + [P, P, P], I32),
+    'pcs_cps_mri_ball_step_c64': ([P] * 6 + [I64, F64, F64, F64, F64, P, P, P], I32),
+    'pcs_cps_mri_ball_step_c128': ([P] * 6 + [I64, F64, F64, F64, F64, P, P, P], I32),
     'pcs_version': ([], I32),
     'pcs_num_sms': ([], I32),
 }

@@ -8,7 +8,8 @@
 //                                                                                 func/penalty.py:134-191, 480-560)
 //     G = None,  dual variable z = [u (m samples) ; w0 ; w1 (N pixels each)],  all complex.
 // One iteration is
-//     S  = Mask^T u                 (pcs_cps_mri_scatter: zero fill + scatter)           [cuFFT: g = DFT^H S]
+//     S  = Mask^T u                 (pcs_cps_mri_scatter: zero fill + scatter; only for the first update of a solve:
+//                                    the ball step of one update leaves Mask^T u' behind for the next)  [cuFFT: g = DFT^H S]
 //     xt = x - tau (g + Grad^T w),  v = 2 xt - x,  x' = rho xt + (1-rho) x
 //     w' = rho fenchel_prox_{sigma lam L21}(w + sigma Grad v) + (1-rho) w                 (pcs_cps_mri_tv_step: one kernel,
 //                                                                                          v through shared memory)
@@ -56,7 +57,7 @@ template <typename R> struct CpsTvArgs {
     V* x_out; V* w_out; V* v_out;
     const V* x; const V* w; const V* g;
     int H, W;
-    R lam, tau, sigma, rho, omr, is0, is1;
+    R lam, tau, sigma, rho, omr, is0, is1, gscale;
     double* partials; unsigned int* ticket; double* diag_out;
 };
 
@@ -75,55 +76,98 @@ __global__ void __launch_bounds__(CPS_NT) cps_tv_kernel(const CpsTvArgs<R> A) {
     double s_dx = 0.0, s_x = 0.0, s_dw = 0.0, s_w = 0.0;
     const V zero = cmake<V, R>(R(0), R(0));
 
+    const V* __restrict__ xin = A.x;
+    const V* __restrict__ gin = A.g;
+    V* __restrict__ xout = A.x_out;
+    V* __restrict__ vout = A.v_out;
+    V* __restrict__ w0out = A.w_out;
+    V* __restrict__ w1out = A.w_out + N;
+    constexpr int UN = sizeof(R) == 4 ? 4 : 2;   // points per thread and batch: all loads of a batch are issued before its arithmetic
+
     for (int tile = blockIdx.x; tile < tiles_w * tiles_h; tile += gridDim.x) {
         const int ti = tile / tiles_w, tj = tile - ti * tiles_w;
         const int i0 = ti * TH, j0 = tj * TW;
         // primal update on the tile plus one row below / one column to the right (the forward differences of v need them)
-        for (int p = tid; p < (TH + 1) * PW; p += CPS_NT) {
-            const int r = p / PW, c = p - r * PW;
-            const int gi = i0 + r, gj = j0 + c;
-            V v = zero;
-            if (gi < H && gj < W) {
-                const int64_t idx = (int64_t)gi * W + gj;
-                const V x = A.x[idx], g = A.g[idx];
+        for (int pb = tid; pb < (TH + 1) * PW; pb += UN * CPS_NT) {
+            V xv[UN], gv[UN], w0c[UN], w0u[UN], w1c[UN], w1l[UN];
+            bool in[UN];
+#pragma unroll
+            for (int k = 0; k < UN; ++k) {
+                const int p = pb + k * CPS_NT;
+                const int r = p / PW, c = p - r * PW;
+                const int gi = i0 + r, gj = j0 + c;
+                in[k] = p < (TH + 1) * PW && gi < H && gj < W;
+                const int64_t idx = in[k] ? (int64_t)gi * W + gj : 0;
+                xv[k] = in[k] ? xin[idx] : zero;
+                gv[k] = in[k] ? gin[idx] : zero;
                 // Gradient^T w (pylops FirstDerivative forward, adjoint: y[:-1] -= z[:-1]/h; y[1:] += z[:-1]/h)
-                const V w0c = gi < H - 1 ? w0[idx] : zero, w0u = gi > 0 ? w0[idx - W] : zero;
-                const V w1c = gj < W - 1 ? w1[idx] : zero, w1l = gj > 0 ? w1[idx - 1] : zero;
-                V a = cscale(csub(w0u, w0c), A.is0);
-                a = caxpy(a, A.is1, csub(w1l, w1c));
-                const V xt = caxpy(x, -A.tau, cadd(g, a));
-                v = caxpy(cscale(x, R(-1)), R(2), xt);
-                if (r < TH && c < TW) {
-                    const V xn = caxpy(cscale(x, A.omr), A.rho, xt);
-                    A.x_out[idx] = xn;
-                    A.v_out[idx] = v;
-                    s_dx += cabs2(csub(xn, x));
-                    s_x += cabs2(x);
+                w0c[k] = (in[k] && gi < H - 1) ? w0[idx] : zero;
+                w0u[k] = (in[k] && gi > 0) ? w0[idx - W] : zero;
+                w1c[k] = (in[k] && gj < W - 1) ? w1[idx] : zero;
+                w1l[k] = (in[k] && gj > 0) ? w1[idx - 1] : zero;
+            }
+#pragma unroll
+            for (int k = 0; k < UN; ++k) {
+                const int p = pb + k * CPS_NT;
+                if (p < (TH + 1) * PW) {
+                    const int r = p / PW, c = p - r * PW;
+                    V v = zero;
+                    if (in[k]) {
+                        const V x = xv[k], g = cscale(gv[k], A.gscale);
+                        V a = cscale(csub(w0u[k], w0c[k]), A.is0);
+                        a = caxpy(a, A.is1, csub(w1l[k], w1c[k]));
+                        const V xt = caxpy(x, -A.tau, cadd(g, a));
+                        v = caxpy(cscale(x, R(-1)), R(2), xt);
+                        if (r < TH && c < TW) {
+                            const int64_t idx = (int64_t)(i0 + r) * W + j0 + c;
+                            const V xn = caxpy(cscale(x, A.omr), A.rho, xt);
+                            xout[idx] = xn;
+                            vout[idx] = v;
+                            s_dx += cabs2(csub(xn, x));
+                            s_x += cabs2(x);
+                        }
+                    }
+                    sv[p] = v;
                 }
             }
-            sv[p] = v;
         }
         __syncthreads();
         // dual update of the TV block: w' = rho P_{lam-ball}(w + sigma Grad v) + (1 - rho) w
         // (fenchel_prox of lam * L21Norm, core/functional.py:207 + func/penalty.py:551-557, in its projection form)
-        for (int p = tid; p < TH * TW; p += CPS_NT) {
-            const int r = p / TW, c = p - r * TW;
-            const int gi = i0 + r, gj = j0 + c;
-            if (gi < H && gj < W) {
-                const int64_t idx = (int64_t)gi * W + gj;
-                const V vc = sv[r * PW + c], vd = sv[(r + 1) * PW + c], vr = sv[r * PW + c + 1];
-                const V d0 = gi < H - 1 ? cscale(csub(vd, vc), A.is0) : zero;
-                const V d1 = gj < W - 1 ? cscale(csub(vr, vc), A.is1) : zero;
-                const V a0 = w0[idx], a1 = w1[idx];
-                const V q0 = caxpy(a0, A.sigma, d0), q1 = caxpy(a1, A.sigma, d1);
-                const R ss = fma(q0.x, q0.x, fma(q0.y, q0.y, fma(q1.x, q1.x, fma(q1.y, q1.y, tiny<R>()))));
-                R f = A.lam * rsq<R>(ss);
-                f = f < R(1) ? f : R(1);
-                const V n0 = caxpy(cscale(a0, A.omr), A.rho * f, q0), n1 = caxpy(cscale(a1, A.omr), A.rho * f, q1);
-                A.w_out[idx] = n0;
-                A.w_out[N + idx] = n1;
-                s_dw += cabs2(csub(n0, a0)) + cabs2(csub(n1, a1));
-                s_w += cabs2(a0) + cabs2(a1);
+        static_assert((TH * TW) % (UN * CPS_NT) == 0, "tile size must be a whole number of batches");
+        for (int pb = tid; pb < TH * TW; pb += UN * CPS_NT) {
+            V a0[UN], a1[UN];
+            bool in[UN];
+#pragma unroll
+            for (int k = 0; k < UN; ++k) {
+                const int p = pb + k * CPS_NT;
+                const int r = p / TW, c = p - r * TW;
+                const int gi = i0 + r, gj = j0 + c;
+                in[k] = gi < H && gj < W;
+                const int64_t idx = in[k] ? (int64_t)gi * W + gj : 0;
+                a0[k] = in[k] ? w0[idx] : zero;
+                a1[k] = in[k] ? w1[idx] : zero;
+            }
+#pragma unroll
+            for (int k = 0; k < UN; ++k) {
+                const int p = pb + k * CPS_NT;
+                const int r = p / TW, c = p - r * TW;
+                const int gi = i0 + r, gj = j0 + c;
+                if (in[k]) {
+                    const int64_t idx = (int64_t)gi * W + gj;
+                    const V vc = sv[r * PW + c], vd = sv[(r + 1) * PW + c], vr = sv[r * PW + c + 1];
+                    const V d0 = gi < H - 1 ? cscale(csub(vd, vc), A.is0) : zero;
+                    const V d1 = gj < W - 1 ? cscale(csub(vr, vc), A.is1) : zero;
+                    const V q0 = caxpy(a0[k], A.sigma, d0), q1 = caxpy(a1[k], A.sigma, d1);
+                    const R ss = fma(q0.x, q0.x, fma(q0.y, q0.y, fma(q1.x, q1.x, fma(q1.y, q1.y, tiny<R>()))));
+                    R f = A.lam * rsq<R>(ss);
+                    f = f < R(1) ? f : R(1);
+                    const V n0 = caxpy(cscale(a0[k], A.omr), A.rho * f, q0), n1 = caxpy(cscale(a1[k], A.omr), A.rho * f, q1);
+                    w0out[idx] = n0;
+                    w1out[idx] = n1;
+                    s_dw += cabs2(csub(n0, a0[k])) + cabs2(csub(n1, a1[k]));
+                    s_w += cabs2(a0[k]) + cabs2(a1[k]);
+                }
             }
         }
         __syncthreads();
@@ -141,9 +185,9 @@ __global__ void __launch_bounds__(CPS_NT) cps_scatter_kernel(typename Cx<R>::typ
 
 template <typename R> struct CpsBallArgs {
     typedef typename Cx<R>::type V;
-    V* u_out; const V* u; const V* spec; const int64_t* idx; const V* y;
+    V* u_out; V* spec_next; const V* u; const V* spec; const int64_t* idx; const V* y;
     int64_t m;
-    R eps, sigma, inv_sigma, rho, omr;
+    R eps, sigma, inv_sigma, rho, omr, vscale;
     double* partials; unsigned int* ticket; double* sumsq; double* tmp; double* diag;
 };
 
@@ -152,7 +196,7 @@ template <typename R> struct CpsBallArgs {
 template <typename R>
 __device__ __forceinline__ void ball_point(const CpsBallArgs<R>& A, int64_t k, typename Cx<R>::type& p,
                                            typename Cx<R>::type& d) {
-    p = caxpy(A.u[k], A.sigma, A.spec[A.idx[k]]);
+    p = caxpy(A.u[k], A.sigma * A.vscale, A.spec[A.idx[k]]);
     d = csub(cscale(p, A.inv_sigma), A.y[k]);
 }
 
@@ -185,6 +229,7 @@ template <typename R> __global__ void __launch_bounds__(CPS_NT) cps_ball_apply_k
         const V uo = A.u[k];
         const V un = caxpy(cscale(uo, A.omr), A.rho, ut);
         A.u_out[k] = un;
+        if (A.spec_next != nullptr) A.spec_next[A.idx[k]] = un;      // Mask^T u' for the next iteration's inverse DFT
         s_du += cabs2(csub(un, uo));
         s_u += cabs2(uo);
     }
@@ -216,8 +261,8 @@ int cps_scatter_impl(void* spec_out, const void* u, const void* idx, int64_t N, 
 
 template <typename R>
 int cps_tv_impl(void* x_out, void* w_out, void* v_out, const void* x, const void* w, const void* g, int64_t H, int64_t W,
-                double lam, double tau, double sigma, double rho, double step0, double step1, double* diag_out,
-                void* workspace, cudaStream_t s) {
+                double gscale, double lam, double tau, double sigma, double rho, double step0, double step1,
+                double* diag_out, void* workspace, cudaStream_t s) {
     typedef typename Cx<R>::type V;
     const char* what = "pcs_cps_mri_tv_step";
     PCS_REQUIRE(H >= 1 && W >= 1 && H < (1ll << 30) && W < (1ll << 30), "%s: bad dimensions", what);
@@ -229,13 +274,14 @@ int cps_tv_impl(void* x_out, void* w_out, void* v_out, const void* x, const void
     A.x = (const V*)x; A.w = (const V*)w; A.g = (const V*)g;
     A.H = (int)H; A.W = (int)W;
     A.lam = (R)lam; A.tau = (R)tau; A.sigma = (R)sigma; A.rho = (R)rho; A.omr = (R)(1 - rho);
-    A.is0 = (R)(1 / step0); A.is1 = (R)(1 / step1);
+    A.is0 = (R)(1 / step0); A.is1 = (R)(1 / step1); A.gscale = (R)gscale;
     A.partials = (double*)workspace;
     A.ticket = (unsigned int*)((double*)workspace + 4 * (size_t)CPS_MAX_BLOCKS);
     A.diag_out = diag_out;
     constexpr int TW = TileW<R>::value;
     const int64_t ntiles = ((H + CPS_TH - 1) / CPS_TH) * ((W + TW - 1) / TW);
-    const int64_t cap = 4 * (int64_t)num_sms() < CPS_MAX_BLOCKS ? 4 * (int64_t)num_sms() : CPS_MAX_BLOCKS;
+    // every tile its own block while the partial-sum slots last (6 blocks of 34 KB fit per SM), else a grid-stride loop
+    const int64_t cap = CPS_MAX_BLOCKS;
     const int grid = (int)(ntiles < cap ? ntiles : cap);
     const size_t smem = (size_t)(CPS_TH + 1) * (TW + 1) * sizeof(V) + 4 * (CPS_NT / 32) * sizeof(double);
     cps_tv_kernel<R><<<grid, CPS_NT, smem, s>>>(A);
@@ -243,17 +289,19 @@ int cps_tv_impl(void* x_out, void* w_out, void* v_out, const void* x, const void
 }
 
 template <typename R>
-int cps_ball_impl(void* u_out, const void* u, const void* spec, const void* idx, const void* y, int64_t m, double eps,
-                  double sigma, double rho, double* diag_inout, void* workspace, cudaStream_t s) {
+int cps_ball_impl(void* u_out, void* spec_next, const void* u, const void* spec, const void* idx, const void* y, int64_t m,
+                  double vscale, double eps, double sigma, double rho, double* diag_inout, void* workspace, cudaStream_t s) {
     typedef typename Cx<R>::type V;
     const char* what = "pcs_cps_mri_ball_step";
     PCS_REQUIRE(m >= 0 && sigma > 0 && eps >= 0, "%s: bad arguments", what);
     PCS_REQUIRE(diag_inout && workspace && (m == 0 || (u_out && u && spec && idx && y)), "%s: null pointer", what);
     if (m == 0) return 0;
     CpsBallArgs<R> A;
-    A.u_out = (V*)u_out; A.u = (const V*)u; A.spec = (const V*)spec; A.idx = (const int64_t*)idx; A.y = (const V*)y;
+    A.u_out = (V*)u_out; A.spec_next = (V*)spec_next; A.u = (const V*)u; A.spec = (const V*)spec; A.idx = (const int64_t*)idx; A.y = (const V*)y;
     A.m = m;
     A.eps = (R)eps; A.sigma = (R)sigma; A.inv_sigma = (R)(1 / sigma); A.rho = (R)rho; A.omr = (R)(1 - rho);
+    A.vscale = (R)vscale;
+    PCS_REQUIRE(spec_next != spec, "%s: spec_next must not alias spec", what);
     double* ws = (double*)workspace;
     A.partials = ws;
     A.ticket = (unsigned int*)(ws + 4 * (size_t)CPS_MAX_BLOCKS);
@@ -281,11 +329,13 @@ PCS_EXPORT_CPLX(pcs_cps_mri_scatter, cps_scatter_impl,
                 (spec_out, u, idx_i64, N, m, (cudaStream_t)stream))
 PCS_EXPORT_CPLX(pcs_cps_mri_tv_step, cps_tv_impl,
                 (void* x_out, void* w_out, void* v_out, const void* x, const void* w, const void* g, int64_t H, int64_t W,
-                 double lam, double tau, double sigma, double rho, double step0, double step1, void* diag_out_f64,
-                 void* workspace, void* stream),
-                (x_out, w_out, v_out, x, w, g, H, W, lam, tau, sigma, rho, step0, step1, (double*)diag_out_f64, workspace,
-                 (cudaStream_t)stream))
+                 double gscale, double lam, double tau, double sigma, double rho, double step0, double step1,
+                 void* diag_out_f64, void* workspace, void* stream),
+                (x_out, w_out, v_out, x, w, g, H, W, gscale, lam, tau, sigma, rho, step0, step1, (double*)diag_out_f64,
+                 workspace, (cudaStream_t)stream))
 PCS_EXPORT_CPLX(pcs_cps_mri_ball_step, cps_ball_impl,
-                (void* u_out, const void* u, const void* spec, const void* idx_i64, const void* y, int64_t m, double eps,
-                 double sigma, double rho, void* diag_inout_f64, void* workspace, void* stream),
-                (u_out, u, spec, idx_i64, y, m, eps, sigma, rho, (double*)diag_inout_f64, workspace, (cudaStream_t)stream))
+                (void* u_out, void* spec_next, const void* u, const void* spec, const void* idx_i64, const void* y,
+                 int64_t m, double vscale, double eps, double sigma, double rho, void* diag_inout_f64, void* workspace,
+                 void* stream),
+                (u_out, spec_next, u, spec, idx_i64, y, m, vscale, eps, sigma, rho, (double*)diag_inout_f64, workspace,
+                 (cudaStream_t)stream))

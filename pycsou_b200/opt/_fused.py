@@ -263,13 +263,17 @@ class CpsMriPlan:
             raise _NoMatch('data size mismatch')
         self.eps, self.lam = float(eps), float(lam)
         self.ws = torch.zeros(int(_lib.call_plain('pcs_cps_mri_workspace_bytes')) // 8, dtype=torch.float64, device=dev)
-        self.spec = torch.empty(self.N, dtype=dt, device=dev)      # Mask^T u, then DFT v
-        self.g = torch.empty(self.N, dtype=dt, device=dev)         # DFT^H Mask^T u
+        self.spec = torch.empty(self.N, dtype=dt, device=dev)      # Mask^T u: scattered once, then kept up to date
         self.v = torch.empty(self.N, dtype=dt, device=dev)         # 2 xt - x
+        self.scale = 1.0 / np.sqrt(float(self.N))                  # the orthonormal scaling is folded into the kernels
+        self._spec_of = None                                       # (data_ptr, version) of the z whose u is in spec
         self._xbuf, self._zbuf = [None, None], [None, None]
 
     _out = PdsTvPlan._out
-    release = PdsTvPlan.release
+
+    def release(self, *tensors):
+        PdsTvPlan.release(self, *tensors)
+        self._spec_of = None             # the caller owns the final z now: its address may come back with other contents
 
     def step(self, x, z, drow):
         s = self.solver
@@ -277,14 +281,18 @@ class CpsMriPlan:
         tau, sigma, rho = float(s.tau), float(s.sigma), float(s.rho)
         xo, zo = self._out(self._xbuf, x), self._out(self._zbuf, z)
         st = K.stream()
-        _lib.call('pcs_cps_mri_scatter' + self.sfx, self.spec.data_ptr(), z.data_ptr(), self.idx.data_ptr(), N, m, st)
-        torch.fft.ifft2(self.spec.view(shp), norm='ortho', out=self.g.view(shp))
+        if self._spec_of != (z.data_ptr(), z._version):
+            _lib.call('pcs_cps_mri_scatter' + self.sfx, self.spec.data_ptr(), z.data_ptr(), self.idx.data_ptr(), N, m, st)
+        # unnormalised transforms (no separate scaling pass): ifft2 'forward' = plain inverse, fft2 'backward' = plain forward
+        g = torch.fft.ifft2(self.spec.view(shp), norm='forward')      # (out= would add a copy pass: torch scales into it)
         _lib.call('pcs_cps_mri_tv_step' + self.sfx, xo.data_ptr(), zo[m:].data_ptr(), self.v.data_ptr(), x.data_ptr(),
-                  z[m:].data_ptr(), self.g.data_ptr(), self.H, self.W, self.lam, tau, sigma, rho, self.steps[0],
-                  self.steps[1], drow.data_ptr(), self.ws.data_ptr(), st)
-        torch.fft.fft2(self.v.view(shp), norm='ortho', out=self.spec.view(shp))
-        _lib.call('pcs_cps_mri_ball_step' + self.sfx, zo.data_ptr(), z.data_ptr(), self.spec.data_ptr(),
-                  self.idx.data_ptr(), self.y.data_ptr(), m, self.eps, sigma, rho, drow.data_ptr(), self.ws.data_ptr(), st)
+                  z[m:].data_ptr(), g.data_ptr(), self.H, self.W, self.scale, self.lam, tau, sigma, rho,
+                  self.steps[0], self.steps[1], drow.data_ptr(), self.ws.data_ptr(), st)
+        V = torch.fft.fft2(self.v.view(shp), norm='backward')
+        _lib.call('pcs_cps_mri_ball_step' + self.sfx, zo.data_ptr(), self.spec.data_ptr(), z.data_ptr(), V.data_ptr(),
+                  self.idx.data_ptr(), self.y.data_ptr(), m, self.scale, self.eps, sigma, rho, drow.data_ptr(),
+                  self.ws.data_ptr(), st)
+        self._spec_of = (zo.data_ptr(), zo._version)
         return xo, zo
 
 
