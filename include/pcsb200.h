@@ -48,6 +48,10 @@ PCS_DECL_REAL(pcs_prox_l21, (void* out, const void* x, double tau, int64_t n_gro
 PCS_DECL_REAL(pcs_scale_by_norm, (void* out, const void* x, const void* sumsq_f64, double param, int mode, int64_t n,
                                   void* stream))
 
+/* the same under the reference's names: L2Norm.prox (mode 0) and proj_l2_ball (mode 1) */
+PCS_DECL_REAL(pcs_prox_l2, (void* out, const void* x, const void* sumsq_f64, double tau, int64_t n, void* stream))
+PCS_DECL_REAL(pcs_proj_l2_ball, (void* out, const void* x, const void* sumsq_f64, double radius, int64_t n, void* stream))
+
 /* ---- deterministic reductions (np.linalg.norm in update_diagnostics, opt/proxalgs.py:366-394; functional values) -- */
 int64_t pcs_reduce_workspace_bytes(void);   /* workspace must be zero-initialised once */
 PCS_DECL_REAL(pcs_reduce_sumsq, (const void* x, int64_t n, void* out_f64, void* workspace, void* stream))
@@ -95,6 +99,15 @@ PCS_DECL_REAL(pcs_conv2d_sep_fwd, (void* out, const void* x, const void* hcol, c
                                    int offset0, int offset1, const void* sub, int64_t H, int64_t W, void* stream))
 PCS_DECL_REAL(pcs_conv2d_sep_adj, (void* out, const void* x, const void* hcol, const void* hrow, int kh, int kw,
                                    int offset0, int offset1, const void* sub, int64_t H, int64_t W, void* stream))
+
+/* FFT path of Convolve2D for large non-separable filters (the reference's default method='fft', linop/conv.py:168 ->
+ * scipy.signal.fftconvolve / correlate): the host runs the padded real transforms (cuFFT), these two kernels do the
+ * rest.  pcs_spectral_mul: a <- a * b (conj_b = 0) or a * conj(b) (conj_b = 1) on n_complex interleaved complex numbers,
+ * in place.  pcs_crop_shift: out[i][j] = scale * full[(i + shift0) mod P0][(j + shift1) mod P1] - sub[i][j] (sub may be
+ * NULL): the "same" crop of the P0 x P1 inverse transform, its normalisation and the residual A x - y in one pass. */
+PCS_DECL_REAL(pcs_spectral_mul, (void* a_inout, const void* b, int conj_b, int64_t n_complex, void* stream))
+PCS_DECL_REAL(pcs_crop_shift, (void* out, const void* full, const void* sub, int64_t H, int64_t W, int64_t P0,
+                               int64_t P1, int64_t shift0, int64_t shift1, double scale, void* stream))
 
 /* ---- sampling: Masking/DownSampling (pycsou/linop/sampling.py:190-196, 362-391), SubSampling = pylops.Restriction
  *      (sampling.py:121).  Elements are opaque 4/8/16-byte words; indices int64, unique for pcs_put ---------------- */

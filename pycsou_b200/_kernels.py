@@ -243,6 +243,24 @@ def conv2d_direct(out, x, h2d, off0, off1, H, W, adjoint=False):
     return out
 
 
+def spectral_mul(a, b, conj_b=False):
+    """a <- a * b or a * conj(b) in place (complex tensors of equal size; csrc/pcs_conv.cu)."""
+    if not (a.is_complex() and b.is_complex() and a.dtype == b.dtype and a.numel() == b.numel()):
+        raise ValueError('spectral_mul needs two complex tensors of the same dtype and size')
+    if not (a.is_contiguous() and b.is_contiguous()):
+        raise ValueError('spectral_mul needs contiguous tensors')
+    _lib.call('pcs_spectral_mul' + sfx(a), ptr(a), ptr(b), int(bool(conj_b)), a.numel(), stream())
+    return a
+
+
+def crop_shift(out, full, H, W, P0, P1, s0, s1, scale, sub=None):
+    """out[i, j] = scale * full[(i + s0) % P0, (j + s1) % P1] - sub[i, j]  (csrc/pcs_conv.cu)."""
+    _chk(out, full, sub)
+    _lib.call('pcs_crop_shift' + sfx(out), ptr(out), ptr(full), ptr(sub), int(H), int(W), int(P0), int(P1), int(s0),
+              int(s1), float(scale), stream())
+    return out
+
+
 def conv2d_sep(out, x, hcol, hrow, off0, off1, H, W, adjoint=False, sub=None):
     _chk(out, x, hcol, hrow, sub)
     name = 'pcs_conv2d_sep_adj' if adjoint else 'pcs_conv2d_sep_fwd'

@@ -34,6 +34,8 @@ REAL = {
     'pcs_reduce_minmax': [P, I64, P, P, P],
     'pcs_reduce_sumgroupnorm': [P, I64, I32, I32, P, P, P],
     'pcs_scale_by_norm': [P, P, P, F64, I32, I64, P],
+    'pcs_prox_l2': [P, P, P, F64, I64, P],
+    'pcs_proj_l2_ball': [P, P, P, F64, I64, P],
     'pcs_firstderiv_fwd': [P, P, I64, I64, I64, I32, I32, F64, I32, P],
     'pcs_firstderiv_adj': [P, P, I64, I64, I64, I32, I32, F64, I32, P],
     'pcs_secondderiv_fwd': [P, P, I64, I64, I64, I32, I32, F64, I32, P],
@@ -48,6 +50,8 @@ REAL = {
     'pcs_conv2d_direct_adj': [P, P, P, I32, I32, I32, I32, I64, I64, P],
     'pcs_conv2d_sep_fwd': [P, P, P, P, I32, I32, I32, I32, P, I64, I64, P],
     'pcs_conv2d_sep_adj': [P, P, P, P, I32, I32, I32, I32, P, I64, I64, P],
+    'pcs_spectral_mul': [P, P, I32, I64, P],
+    'pcs_crop_shift': [P, P, P, I64, I64, I64, I64, I64, I64, F64, P],
     # fused Condat-Vu TV iteration (csrc/pcs_pds.cu); argument order as in include/pcsb200.h
     'pcs_pds_tv_step': [P] * 5 + [I64] * 6 + [I32, I32, P, P, P] + [I32] * 4 + [I32, F64, F64, I32] + [F64] * 6 +
                        [I32] * 3 + [P, P, P],

@@ -10,6 +10,7 @@
 //   conv2d sep.  rank-1 filter (h = hcol (x) hrow): row pass and column pass through one shared-memory tile;
 //                optional fused "- y" (residual r = A x - y of the data term).
 #include "pcs_common.cuh"
+#include <type_traits>
 
 using namespace pcs;
 
@@ -252,3 +253,76 @@ static int pcs_conv2d_sep_adj_impl(T* o, const T* x, const T* hc, const T* hr, i
 PCS_EXPORT_REAL(pcs_conv2d_sep_adj, C2S_PARAMS,
                 ((T*)out, (const T*)x, (const T*)hcol, (const T*)hrow, kh, kw, offset0, offset1, (const T*)sub, H, W,
                  (cudaStream_t)stream))
+
+// ---- FFT path for large non-separable PSFs ---------------------------------------------------------------------------
+// Convolve2D's default method in the reference is 'fft' (pycsou/linop/conv.py:168 -> scipy.signal.fftconvolve /
+// correlate(method='fft')).  Here the transforms are library calls made by the host (cuFFT through torch.fft, where the
+// reference calls pocketfft); the work around them is fused into two kernels of this library:
+//   pcs_spectral_mul: X <- X * Hf or X * conj(Hf) in place on the half spectrum (forward / adjoint), and
+//   pcs_crop_shift:   out[i][j] = scale * full[(i + s0) mod P0][(j + s1) mod P1] - sub[i][j], i.e. the "same" crop of the
+//                     padded inverse transform, its 1/(P0 P1) normalisation and the data-term residual A x - y in one pass.
+namespace {
+template <typename R>
+__global__ void __launch_bounds__(256) spectral_mul_kernel(R* __restrict__ a, const R* __restrict__ b, int conj_b, int64_t n) {
+    typedef typename std::conditional<sizeof(R) == 4, float2, double2>::type V;
+    V* av = reinterpret_cast<V*>(a);
+    const V* bv = reinterpret_cast<const V*>(b);
+    const R sg = conj_b ? R(-1) : R(1);
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += (int64_t)gridDim.x * blockDim.x) {
+        const V x = av[k], h = bv[k];
+        const R hi = sg * h.y;
+        V r;
+        r.x = x.x * h.x - x.y * hi;
+        r.y = x.x * hi + x.y * h.x;
+        av[k] = r;
+    }
+}
+template <typename T>
+__global__ void __launch_bounds__(256) crop_shift_kernel(T* __restrict__ out, const T* __restrict__ full,
+                                                         const T* __restrict__ sub, int H, int W, int P0, int P1, int s0,
+                                                         int s1, T scale) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= W) return;
+    int fj = j + s1;
+    fj = fj < 0 ? fj + P1 : (fj >= P1 ? fj - P1 : fj);
+    for (int i = blockIdx.y; i < H; i += gridDim.y) {
+        int fi = i + s0;
+        fi = fi < 0 ? fi + P0 : (fi >= P0 ? fi - P0 : fi);
+        T v = scale * full[(int64_t)fi * P1 + fj];
+        if (sub != nullptr) v -= sub[(int64_t)i * W + j];
+        out[(int64_t)i * W + j] = v;
+    }
+}
+}  // namespace
+
+template <typename T>
+static int pcs_spectral_mul_impl(T* a, const T* b, int conj_b, int64_t n, cudaStream_t s) {
+    const char* what = "pcs_spectral_mul";
+    PCS_REQUIRE(n >= 0, "%s: bad size", what);
+    if (n == 0) return PCS_OK;
+    PCS_REQUIRE(a && b, "%s: null pointer", what);
+    PCS_REQUIRE(((uintptr_t)a % (2 * sizeof(T))) == 0 && ((uintptr_t)b % (2 * sizeof(T))) == 0, "%s: unaligned complex array", what);
+    const int64_t nb = (n + 255) / 256, cap = 8 * (int64_t)num_sms();
+    spectral_mul_kernel<T><<<(unsigned)(nb < cap ? nb : cap), 256, 0, s>>>(a, b, conj_b, n);
+    return check_launch(what);
+}
+PCS_EXPORT_REAL(pcs_spectral_mul, (void* a_inout, const void* b, int conj_b, int64_t n_complex, void* stream),
+                ((T*)a_inout, (const T*)b, conj_b, n_complex, (cudaStream_t)stream))
+
+template <typename T>
+static int pcs_crop_shift_impl(T* out, const T* full, const T* sub, int64_t H, int64_t W, int64_t P0, int64_t P1,
+                               int64_t s0, int64_t s1, double scale, cudaStream_t s) {
+    const char* what = "pcs_crop_shift";
+    PCS_REQUIRE(H >= 0 && W >= 0 && P0 >= H && P1 >= W && P0 < (1ll << 30) && P1 < (1ll << 30), "%s: bad dimensions", what);
+    PCS_REQUIRE(s0 > -P0 && s0 < P0 && s1 > -P1 && s1 < P1 && H + (s0 > 0 ? s0 : 0) <= 2 * P0 && W + (s1 > 0 ? s1 : 0) <= 2 * P1,
+                "%s: shift outside the padded array", what);
+    if (H * W == 0) return PCS_OK;
+    PCS_REQUIRE(out && full && out != full, "%s: null or aliased pointer", what);
+    dim3 grid((unsigned)((W + 255) / 256), (unsigned)(H < 4096 ? H : 4096));
+    crop_shift_kernel<T><<<grid, 256, 0, s>>>(out, full, sub, (int)H, (int)W, (int)P0, (int)P1, (int)s0, (int)s1, (T)scale);
+    return check_launch(what);
+}
+PCS_EXPORT_REAL(pcs_crop_shift,
+                (void* out, const void* full, const void* sub, int64_t H, int64_t W, int64_t P0, int64_t P1, int64_t shift0,
+                 int64_t shift1, double scale, void* stream),
+                ((T*)out, (const T*)full, (const T*)sub, H, W, P0, P1, shift0, shift1, scale, (cudaStream_t)stream))

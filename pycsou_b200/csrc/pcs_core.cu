@@ -395,3 +395,18 @@ static int pcs_scale_by_norm_impl(T* out, const T* x, const double* sumsq, doubl
 PCS_EXPORT_REAL(pcs_scale_by_norm,
                 (void* out, const void* x, const void* sumsq_f64, double param, int mode, int64_t n, void* stream),
                 ((T*)out, (const T*)x, (const double*)sumsq_f64, param, mode, n, (cudaStream_t)stream))
+
+// L2Norm.prox (func/penalty.py:23-70 through LpNorm.prox, func/base.py:215-240) and proj_l2_ball (math/prox.py:167-210)
+// under the names SURVEY.md 8(b) lists: thin wrappers of pcs_scale_by_norm (sumsq_f64 = ||x||^2 from pcs_reduce_sumsq).
+template <typename T>
+static int pcs_prox_l2_impl(T* out, const T* x, const double* sumsq, double tau, int64_t n, cudaStream_t s) {
+    return pcs_scale_by_norm_impl<T>(out, x, sumsq, tau, 0, n, s);
+}
+PCS_EXPORT_REAL(pcs_prox_l2, (void* out, const void* x, const void* sumsq_f64, double tau, int64_t n, void* stream),
+                ((T*)out, (const T*)x, (const double*)sumsq_f64, tau, n, (cudaStream_t)stream))
+template <typename T>
+static int pcs_proj_l2_ball_impl(T* out, const T* x, const double* sumsq, double radius, int64_t n, cudaStream_t s) {
+    return pcs_scale_by_norm_impl<T>(out, x, sumsq, radius, 1, n, s);
+}
+PCS_EXPORT_REAL(pcs_proj_l2_ball, (void* out, const void* x, const void* sumsq_f64, double radius, int64_t n, void* stream),
+                ((T*)out, (const T*)x, (const double*)sumsq_f64, radius, n, (cudaStream_t)stream))

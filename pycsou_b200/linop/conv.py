@@ -5,11 +5,15 @@ keep the reference's signatures and its centring rule (filter centred at ``n//2`
 ones, ``conv.py:159-162, 285-293``): zero-padded "same" convolution forward, correlation (the exact transpose) in
 adjoint mode.  The reference evaluates them with ``scipy.signal`` (direct or pocketfft); here compact filters run on
 direct shared-memory stencil kernels, and a 2-D filter that is numerically rank-1 (e.g. any Gaussian) is detected by
-SVD at construction and applied as a row pass + column pass (``csrc/pcs_conv.cu``).  ``method`` is validated as in
-pylops but does not change the arithmetic path; results agree with either scipy method to rounding.
+SVD at construction and applied as a row pass + column pass (``csrc/pcs_conv.cu``).  Large non-separable 2-D filters
+(more than 15 x 15 taps) take an FFT path: padded real transforms by cuFFT (where the reference calls pocketfft), the
+spectral multiply and the crop + normalisation + residual ``A x - y`` fused into two kernels of this library.
+``method`` is validated as in pylops but does not select the arithmetic path; results agree with either scipy method
+to rounding.
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Union
 
 import numpy as np
@@ -22,6 +26,7 @@ from ..core.linop import LinearOperator
 __all__ = ['Convolve1D', 'Convolve2D', 'MovingAverage1D', 'MovingAverage2D']
 
 SEPARABLE_RTOL = 1e-13     # second singular value / first below this -> treated as exactly rank-1
+FFT_MIN_TAPS = 15 * 15     # non-separable filters with more taps than this take the FFT path
 
 
 def _centre(n: int) -> int:
@@ -90,7 +95,35 @@ class Convolve2DOperator(LinearOperator):
             if self.hcol.sum() < 0:
                 self.hcol, self.hrow = -self.hcol, -self.hrow
         self._taps = {}
+        # Large non-separable filters: direct evaluation costs kh*kw FMA per pixel (and the tile no longer fits in shared
+        # memory beyond ~100 x 100 taps); they take the FFT path (padded real transforms by cuFFT, spectral multiply
+        # and crop / normalisation / residual fused into two kernels of this library).  PCS_CONV2D_PATH=fft|direct forces one.
+        forced = os.environ.get('PCS_CONV2D_PATH', '')
+        self.use_fft = (not self.is_separable) and (forced == 'fft' or (forced != 'direct' and h.size > FFT_MIN_TAPS))
+        if self.use_fft:
+            from scipy.fft import next_fast_len
+            H, W = self.array_shape
+            self.padded = (int(next_fast_len(H + h.shape[0] - 1, real=True)), int(next_fast_len(W + h.shape[1] - 1, real=True)))
+        self._spectrum = {}
         super().__init__(shape=(size, size), dtype=np.dtype(dtype))
+
+    def _hf(self, like):
+        """Half spectrum of the zero-padded filter (once per dtype / device)."""
+        key = (like.dtype, like.device)
+        if key not in self._spectrum:
+            h = to_device(self.filter, like.dtype).reshape(self.filter.shape)
+            self._spectrum[key] = torch.fft.rfft2(h, s=self.padded).contiguous()
+        return self._spectrum[key]
+
+    def _run_fft(self, x, adjoint, sub):
+        H, W = self.array_shape
+        P0, P1 = self.padded
+        X = torch.fft.rfft2(x.view(H, W), s=(P0, P1)).contiguous()           # (no copy when cuFFT's layout is already dense)
+        K.spectral_mul(X, self._hf(x), conj_b=adjoint)
+        full = torch.fft.irfft2(X, s=(P0, P1), norm='forward')              # unnormalised: 1/(P0 P1) is applied by the crop
+        # forward: y[i] = full[i + off]; adjoint (correlation): y[i] = c[i - off], indices wrapping into the zero padding
+        s0, s1 = (-self.offset[0], -self.offset[1]) if adjoint else self.offset
+        return K.crop_shift(torch.empty_like(x), full.contiguous().reshape(-1), H, W, P0, P1, s0, s1, 1.0 / (P0 * P1), sub=sub)
 
     def _dev(self, like):
         key = (like.dtype, like.device)
@@ -105,6 +138,8 @@ class Convolve2DOperator(LinearOperator):
         if x.is_complex():
             raise NotImplementedError('complex Convolve2D')
         H, W = self.array_shape
+        if self.use_fft:
+            return self._run_fft(x, adjoint, sub)
         t = self._dev(x)
         out = torch.empty_like(x)
         if self.is_separable:

@@ -220,3 +220,44 @@ def test_torch_in_torch_out_and_errors():
     with pytest.raises(ValueError):
         from pycsou_b200 import _kernels as K
         K.grad2d(x, x, 8, 8, 'forward', True, 1, 1)     # aliased stencil output
+
+
+@pytest.mark.parametrize('dtype,tol', [('float64', 1e-12), ('float32', 2e-5)])
+@pytest.mark.parametrize('shape,kshape', [((70, 90), (21, 17)), ((64, 64), (32, 30)), ((40, 130), (9, 7)), ((33, 35), (33, 35))])
+def test_convolve2d_fft_path_matches_oracle(shape, kshape, dtype, tol, monkeypatch):
+    """Large non-separable PSFs take the FFT path (cuFFT + fused spectral multiply / crop kernels): forward, adjoint and
+    the fused residual against the scipy-based oracle; odd and even filter sizes; a filter as large as the image."""
+    import torch
+    from oracle import np_oracle as O
+    from pycsou_b200.linop.conv import Convolve2D
+    monkeypatch.setenv('PCS_CONV2D_PATH', 'fft' if kshape[0] * kshape[1] <= 225 else '')
+    rng = np.random.default_rng(3)
+    N = shape[0] * shape[1]
+    h = rng.random(kshape) + 0.05
+    h /= h.sum()
+    A = Convolve2D(size=N, filter=h, shape=shape, dtype=dtype)
+    assert A.use_fft and not A.is_separable
+    Ao = O.Convolve2D(N, h, shape)
+    x, y = rng.standard_normal(N).astype(dtype), rng.standard_normal(N).astype(dtype)
+    assert rel_l2(A(x), Ao.matvec(x.astype(np.float64))) < tol
+    assert rel_l2(A.adjoint(y), Ao.rmatvec(y.astype(np.float64))) < tol
+    xd, yd = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    r = A._residual(xd, yd).cpu().numpy()
+    assert rel_l2(r, Ao.matvec(x.astype(np.float64)) - y) < tol
+    # adjointness <A x, y> = <x, A^T y>
+    lhs, rhs = float(np.dot(A(x).astype(np.float64), y)), float(np.dot(x, A.adjoint(y).astype(np.float64)))
+    assert abs(lhs - rhs) <= (1e-10 if dtype == 'float64' else 1e-3) * max(1.0, abs(lhs))
+
+
+def test_convolve2d_fft_and_direct_paths_agree(monkeypatch):
+    from pycsou_b200.linop.conv import Convolve2D
+    rng = np.random.default_rng(4)
+    shape, N = (50, 60), 3000
+    h = rng.random((11, 13))
+    x = rng.standard_normal(N)
+    monkeypatch.setenv('PCS_CONV2D_PATH', 'direct')
+    Ad = Convolve2D(size=N, filter=h, shape=shape)
+    monkeypatch.setenv('PCS_CONV2D_PATH', 'fft')
+    Af = Convolve2D(size=N, filter=h, shape=shape)
+    assert Af.use_fft and not Ad.use_fft
+    assert rel_l2(Af(x), Ad(x)) < 1e-13 and rel_l2(Af.adjoint(x), Ad.adjoint(x)) < 1e-13
