@@ -18,6 +18,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import weakref
 from numbers import Number
 
 import numpy as np
@@ -154,7 +155,7 @@ class PdsTvPlan:
     """One-launch-per-iteration Condat-Vu TV solver state (device buffers, filter taps, workspace)."""
 
     def __init__(self, solver, H, W, steps, data_mode, y, A, g, h):
-        self.solver = solver
+        self.solver = weakref.proxy(solver)      # no reference cycle: the solver (and its result buffers) die by refcount
         self.H, self.W, self.steps = H, W, steps
         self.data_mode = data_mode
         self.g_mode, self.g_a, self.g_b = g
@@ -249,7 +250,7 @@ class CpsMriPlan:
     """
 
     def __init__(self, solver, H, W, steps, mask_op, dft, y, eps, lam):
-        self.solver = solver
+        self.solver = weakref.proxy(solver)      # no reference cycle: the solver (and its result buffers) die by refcount
         self.H, self.W, self.steps = H, W, steps
         self.N, self.m = H * W, int(mask_op.nb_of_samples)
         dt = solver._dtype
@@ -369,7 +370,7 @@ class ApgdConv1dPlan:
 
     def __init__(self, solver, A, y, g_mode, g_param):
         dt = solver._dtype
-        self.solver, self.dtype = solver, dt
+        self.solver, self.dtype = weakref.proxy(solver), dt
         self.sfx = '_f32' if dt == torch.float32 else '_f64'
         self.y = to_device(y, dt)
         self.h = to_device(A.filter, dt)

@@ -30,6 +30,8 @@ from __future__ import annotations
 import ctypes as C
 
 import numpy as np
+import weakref
+
 import torch
 import torch.distributed as dist
 
@@ -276,7 +278,7 @@ class SlabPdsTvPlan:
         from .. import _kernels as K
         from .. import _lib
         from .._array import to_device
-        self.solver, self.comm = solver, comm
+        self.solver, self.comm = weakref.proxy(solver), comm
         self.lay = lay = comm.layout(Hg, W)
         self.steps, self.data_mode = steps, data_mode
         self.g_mode, self.g_a, self.g_b = g
