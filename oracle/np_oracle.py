@@ -543,6 +543,21 @@ def Convolve2D(size, filter, shape, dtype='float64', method='fft'):
                          offset=(_offset(filter.shape[0]), _offset(filter.shape[1])))
 
 
+def MovingAverage1D(window_size, shape, axis=0, dtype='float64'):
+    """linop/conv.py:298-350 -> pylops.Smoothing1D(nsmooth, dims, dir): Convolve1D with ones(n)/n, n made odd, centred."""
+    n = window_size + 1 if window_size % 2 == 0 else window_size
+    shape = tuple(np.atleast_1d(shape))
+    return pl.Convolve1D(N=int(np.prod(shape)), h=np.ones(n) / n, dims=shape if len(shape) > 1 else None, dir=axis,
+                         dtype=dtype, method=None, offset=(n - 1) // 2)
+
+
+def MovingAverage2D(window_shape, shape, dtype='float64'):
+    """linop/conv.py:351-418 -> pylops.Smoothing2D(nsmooth, dims): Convolve2D with ones/(n0 n1), sizes made odd."""
+    n0, n1 = (w + 1 if w % 2 == 0 else w for w in window_shape)
+    return pl.Convolve2D(N=int(np.prod(shape)), h=np.ones((n0, n1)) / (n0 * n1), dims=shape, nodir=None, dtype=dtype,
+                         method='fft', offset=((n0 - 1) // 2, (n1 - 1) // 2))
+
+
 def SubSampling(size, sampling_indices, shape=None, axis=0, dtype='float64', inplace=True):
     """linop/sampling.py:25-122."""
     return pl.Restriction(M=size, iava=sampling_indices, dims=shape, dir=axis, dtype=dtype, inplace=inplace)

@@ -169,9 +169,23 @@ def Convolve2D(size: int, filter, shape: tuple, dtype: type = 'float64', method:
     return Convolve2DOperator(size, filter, shape, dtype, method)
 
 
-def MovingAverage1D(*args, **kwargs):
-    raise NotImplementedError('MovingAverage1D is outside the B200 hot path (SURVEY.md section 2)')
+def _odd(n: int) -> int:
+    n = int(n)
+    return n + 1 if n % 2 == 0 else n       # pylops.Smoothing1D / Smoothing2D make the window odd
 
 
-def MovingAverage2D(*args, **kwargs):
-    raise NotImplementedError('MovingAverage2D is outside the B200 hot path (SURVEY.md section 2)')
+def MovingAverage1D(window_size: int, shape: tuple, axis: int = 0, dtype='float64') -> LinearOperator:
+    r"""Moving average along ``axis`` (reference ``conv.py:298-350`` -> ``pylops.Smoothing1D``): a ``Convolve1D`` with
+    the constant filter ``ones(n)/n`` (``n`` made odd), centred; self-adjoint away from the array ends."""
+    n = _odd(window_size)
+    shape = tuple(int(v) for v in np.atleast_1d(shape))
+    size = int(np.prod(shape))
+    return Convolve1DOperator(size, np.full(n, 1.0 / n), shape if len(shape) > 1 else None, axis, dtype, None)
+
+
+def MovingAverage2D(window_shape: Union[tuple, list], shape: tuple, dtype='float64') -> LinearOperator:
+    r"""2-D moving average (reference ``conv.py:351-418`` -> ``pylops.Smoothing2D``): a ``Convolve2D`` with the
+    constant (rank-1, hence separable) filter ``ones(n0, n1) / (n0 n1)``, window sizes made odd."""
+    n0, n1 = _odd(window_shape[0]), _odd(window_shape[1])
+    size = int(np.prod(shape))
+    return Convolve2DOperator(size, np.full((n0, n1), 1.0 / (n0 * n1)), tuple(shape), dtype, 'fft')

@@ -261,3 +261,24 @@ def test_convolve2d_fft_and_direct_paths_agree(monkeypatch):
     Af = Convolve2D(size=N, filter=h, shape=shape)
     assert Af.use_fft and not Ad.use_fft
     assert rel_l2(Af(x), Ad(x)) < 1e-13 and rel_l2(Af.adjoint(x), Ad.adjoint(x)) < 1e-13
+
+
+def test_moving_average_operators():
+    """MovingAverage1D / MovingAverage2D (reference conv.py:298-418) against the oracle; even windows become odd."""
+    from pycsou_b200.linop.conv import MovingAverage1D, MovingAverage2D
+    r = rng(9)
+    for win, shape, axis in ((5, (300,), 0), (4, (40, 30), 0), (7, (40, 30), 1), (3, (6, 20, 10), 1)):
+        n = int(np.prod(shape))
+        x = r.standard_normal(n)
+        A, Ao = MovingAverage1D(win, shape, axis=axis), O.MovingAverage1D(win, shape, axis=axis)
+        assert A.shape == (n, n)
+        assert rel_l2(A(x), Ao.matvec(x)) < 1e-13 and rel_l2(A.adjoint(x), Ao.rmatvec(x)) < 1e-13
+    for win, shape in (((5, 3), (40, 50)), ((4, 6), (33, 47))):
+        n = shape[0] * shape[1]
+        x = r.standard_normal(n)
+        A, Ao = MovingAverage2D(win, shape), O.MovingAverage2D(win, shape)
+        assert A.is_separable
+        assert rel_l2(A(x), Ao.matvec(x)) < 1e-13 and rel_l2(A.adjoint(x), Ao.rmatvec(x)) < 1e-13
+    # constant signal: the interior is reproduced exactly (the window sums to one)
+    y = MovingAverage1D(5, (50,))(np.ones(50))
+    assert np.allclose(y[2:-2], 1.0) and y[0] < 1.0
