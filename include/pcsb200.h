@@ -144,6 +144,17 @@ PCS_DECL_REAL(pcs_pds_tv_step,
                double step0, double step1, int strip_cols, int nseg, int use_tma, void* diag_out_f64, void* workspace,
                void* stream))
 
+/* n_iters consecutive updates enqueued by one call: update k reads buffer pair (k & 1 ? b : a), writes the other one
+ * and puts its four sums in row k of diag_out_f64 (n_iters x 4 doubles).  The result is in pair a when n_iters is even.
+ * For the part of GenericIterativeAlgorithm.iterate (core/solver.py:64-76) in which no stop test can fire (up to
+ * min_iter).  Not for data_mode 3. */
+PCS_DECL_REAL(pcs_pds_tv_run,
+              (void* x_a, void* z_a, void* x_b, void* z_b, const void* b, int64_t H, int64_t W, int data_mode, int ntaps,
+               const double* crow_host, const double* ccol_host, const void* edge, int nl, int nr, int nt, int nb,
+               int g_mode, double g_a, double g_b, int h_mode, double lam, double tau, double sigma, double rho,
+               double step0, double step1, int strip_cols, int nseg, int use_tma, int64_t n_iters, void* diag_out_f64,
+               void* workspace, void* stream))
+
 /* ---- fused ChambollePockSplitting iteration for compressed-sensing MRI with a TV penalty (complex data):
  *      PrimalDualSplitting.update_iterand + update_diagnostics (pycsou/opt/proxalgs.py:343-394, CPS :628-713) for
  *        K = LinOpVStack(Masking * DFT, Gradient(kind='forward'))   (linop/base.py:159-314, sampling.py:125-196,

@@ -55,6 +55,8 @@ REAL = {
     # fused Condat-Vu TV iteration (csrc/pcs_pds.cu); argument order as in include/pcsb200.h
     'pcs_pds_tv_step': [P] * 5 + [I64] * 6 + [I32, I32, P, P, P] + [I32] * 4 + [I32, F64, F64, I32] + [F64] * 6 +
                        [I32] * 3 + [P, P, P],
+    'pcs_pds_tv_run': [P] * 5 + [I64, I64] + [I32, I32, P, P, P] + [I32] * 4 + [I32, F64, F64, I32] + [F64] * 6 +
+                      [I32] * 3 + [I64, P, P, P],
     # a whole APGD solve (flat Convolve1D data term) in one launch (csrc/pcs_apgd.cu)
     'pcs_apgd_conv1d_run': [P, P, P, P, I32, I32, I64, I32, F64, F64, I32, F64, F64, I64, I64, I64, F64, P, P, P],
     # ... fused with the halo push / flag handshake of the slab decomposition (last argument: HOST int64[18])

@@ -235,6 +235,24 @@ class PdsTvPlan:
         return xo, zo
 
 
+def _run_many(self, x, z, n, drows):
+    """``n`` consecutive updates enqueued by ONE library call (``pcs_pds_tv_run``); ``drows``: n x 4 diagnostics rows."""
+    s = self.solver
+    xo, zo = self._out(self._xbuf, x), self._out(self._zbuf, z)
+    crow = self.crow.ctypes.data_as(C.c_void_p) if self.crow is not None else None
+    ccol = self.ccol.ctypes.data_as(C.c_void_p) if self.ccol is not None else None
+    _lib.call('pcs_pds_tv_run' + self.sfx, x.data_ptr(), z.data_ptr(), xo.data_ptr(), zo.data_ptr(), K.ptr(self.b),
+              self.H, self.W, self.data_mode, self.ntaps, crow, ccol, K.ptr(self.edge), self.nl, self.nr, self.nt, self.nb,
+              self.g_mode, self.g_a, self.g_b, self.h_mode, self.lam, float(s.tau), float(s.sigma), float(s.rho),
+              self.steps[0], self.steps[1], self.strip_cols, self.nseg, self.use_tma, int(n), drows.data_ptr(),
+              self.ws.data_ptr(), K.stream())
+    _lib.launch_count += int(n) - 1                      # one call, n kernel launches
+    return (x, z) if n % 2 == 0 else (xo, zo)
+
+
+PdsTvPlan.run_many = _run_many
+
+
 def K_device():
     from .._array import device
     return device()

@@ -22,6 +22,8 @@ from __future__ import annotations
 from numbers import Number
 from typing import Any, Optional, Tuple
 
+import os
+
 import numpy as np
 import torch
 
@@ -87,6 +89,17 @@ class _DeviceLoop:
         it = 0
         spec = None                          # speculative (state, it) already launched for index `it`
         while True:
+            # Updates up to min_iter run unconditionally (core/solver.py:65-66): a plan that can enqueue several updates
+            # with one library call does so (no per-update Python / ctypes work between the kernels).
+            if spec is None and self.verbose is None and it <= self.min_iter:
+                n = int(self.min_iter) + 1 - it
+                many = self._step_many(state, it, n) if n >= 2 else None
+                if many is not None:
+                    state = many
+                    it += n
+                    if self.min_iter < it <= self.max_iter:
+                        self._post_metric_copy(it - 1)
+                    continue
             if it <= self.min_iter:
                 go = True
             elif it > self.max_iter:
@@ -122,6 +135,10 @@ class _DeviceLoop:
 
     def _reduce_diag(self, n):
         """Hook for distributed solvers: sum the per-rank partial norms of rows [0, n) (single GPU: nothing)."""
+
+    def _step_many(self, state, it, n):
+        """Hook: updates it .. it+n-1 enqueued by one call; returns the new state, or None (one call per update)."""
+        return None
 
     def _primal_metric(self, it):
         d = self._diag_host[it]
@@ -300,6 +317,13 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
         if self._plan is not None:
             return self._plan.step(x, z, self._diag_dev[it])
         return self._generic_step(x, z, self._diag_dev[it])
+
+    def _step_many(self, state, it, n):
+        plan = self._plan
+        if (plan is None or self._slab is not None or not hasattr(plan, 'run_many') or getattr(plan, 'data_mode', 3) == 3
+                or os.environ.get('PCS_PDS_BATCH', '1') == '0'):        # debug switch: one library call per update
+            return None
+        return plan.run_many(state[0], state[1], n, self._diag_dev[it:it + n])
 
     def _make_plan(self):
         if self._slab is not None:
