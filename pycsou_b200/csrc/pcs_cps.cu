@@ -21,6 +21,10 @@
 // HBM traffic per iteration outside the FFTs: read x, g, w (4 N), write x', w', v (4 N), S (N + m) and 6 m for the ball step.
 #include "pcs_common.cuh"
 #include <math.h>
+#include <stdlib.h>
+#include <cooperative_groups.h>
+
+namespace cg = cooperative_groups;
 
 using namespace pcs;
 
@@ -241,6 +245,72 @@ template <typename R> __global__ void __launch_bounds__(CPS_NT) cps_ball_apply_k
     }
 }
 
+// One-kernel form of the ball step (cooperative launch: every block resident, one grid-wide barrier).  A block keeps
+// p = u + sigma V[mask] and the grid index of its samples in SHARED memory across the barrier (12 / 20 bytes per sample,
+// up to spt samples per thread), so the gather V[mask] and the 8-byte index list are read ONCE instead of twice; u and
+// y (coalesced) are read again.  The norm is summed in a fixed order (per-block partials, then every block adds up all of
+// them in the same order): deterministic, and identical in all blocks.
+template <typename R> __global__ void __launch_bounds__(CPS_NT) cps_ball_fused_kernel(const CpsBallArgs<R> A, int spt) {
+    typedef typename Cx<R>::type V;
+    extern __shared__ __align__(16) unsigned char smem[];
+    V* const sp = reinterpret_cast<V*>(smem);                                        // [spt][CPS_NT]
+    int* const sgi = reinterpret_cast<int*>(smem + (size_t)spt * CPS_NT * sizeof(V));  // [spt][CPS_NT]
+    __shared__ double red[2 * (CPS_NT / 32)];
+    __shared__ double s_total;
+    cg::grid_group grid = cg::this_grid();
+    const int tid = threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * CPS_NT, k0 = blockIdx.x * (int64_t)CPS_NT + tid;
+    double acc = 0.0;
+#pragma unroll 4
+    for (int q = 0; q < spt; ++q) {
+        const int64_t k = k0 + q * stride;
+        if (k < A.m) {
+            const int64_t g = A.idx[k];
+            const V p = caxpy(A.u[k], A.sigma * A.vscale, A.spec[g]);
+            sp[q * CPS_NT + tid] = p;
+            sgi[q * CPS_NT + tid] = (int)g;
+            acc += cabs2(csub(cscale(p, A.inv_sigma), A.y[k]));
+        }
+    }
+    double v1[1] = {acc};
+    block_sum<1, CPS_NT>(v1, red);
+    if (tid == 0) A.partials[blockIdx.x] = v1[0];
+    grid.sync();
+    double t = 0.0;
+    for (int i = tid; i < (int)gridDim.x; i += CPS_NT) t += __ldcg(&A.partials[i]);
+    double v1b[1] = {t};
+    __syncthreads();
+    block_sum<1, CPS_NT>(v1b, red);
+    if (tid == 0) s_total = v1b[0];
+    __syncthreads();
+    const double nrm = sqrt(s_total);
+    const bool inside = nrm <= (double)A.eps;
+    const R f = inside ? R(1) : (R)((double)A.eps / nrm);
+    double s_du = 0.0, s_u = 0.0;
+#pragma unroll 4
+    for (int q = 0; q < spt; ++q) {
+        const int64_t k = k0 + q * stride;
+        if (k < A.m) {
+            const V p = sp[q * CPS_NT + tid], yk = A.y[k], uo = A.u[k];
+            const V d = csub(cscale(p, A.inv_sigma), yk);
+            const V prox = cadd(inside ? d : cscale(d, f), yk);
+            const V ut = caxpy(p, -A.sigma, prox);
+            const V un = caxpy(cscale(uo, A.omr), A.rho, ut);
+            A.u_out[k] = un;
+            if (A.spec_next != nullptr) A.spec_next[sgi[q * CPS_NT + tid]] = un;
+            s_du += cabs2(csub(un, uo));
+            s_u += cabs2(uo);
+        }
+    }
+    grid.sync();                               // every block has read the norm partials: the slots can be reused
+    double v2[2] = {s_du, s_u};
+    const bool last = grid_sum_finish<2, CPS_NT>(v2, A.partials, A.ticket, A.tmp, red);
+    if (last && tid == 0) {
+        A.diag[2] += A.tmp[0];
+        A.diag[3] += A.tmp[1];
+    }
+}
+
 // workspace (doubles): [0, 4 MAXB) partial sums | ticket | tmp[4] | sumsq
 constexpr size_t CPS_WS_DOUBLES = 4 * (size_t)CPS_MAX_BLOCKS + 8;
 
@@ -311,6 +381,33 @@ int cps_ball_impl(void* u_out, void* spec_next, const void* u, const void* spec,
     const int64_t nb = (m + CPS_NT - 1) / CPS_NT;
     const int64_t cap = 8 * (int64_t)num_sms() < CPS_MAX_BLOCKS ? 8 * (int64_t)num_sms() : CPS_MAX_BLOCKS;
     const int grid = (int)(nb < cap ? nb : cap);
+    // one cooperative kernel when the samples fit in the shared memory of one resident wave, else norm pass + update pass
+    static const bool no_coop = [] { const char* e = getenv("PCS_CPS_BALL_TWO_PASS"); return e && atoi(e) != 0; }();
+    if (!no_coop) {                            // (grid indices are kept as int32: images below 2^31 pixels)
+        const size_t per_sample = sizeof(V) + sizeof(int);
+        for (int spt = 1; spt <= 16; ++spt) {
+            const size_t smem = (size_t)spt * CPS_NT * per_sample;
+            if (smem > 96 * 1024) break;
+            int per_sm = 0;
+            if (smem > 48 * 1024)
+                cudaFuncSetAttribute(cps_ball_fused_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cps_ball_fused_kernel<R>, CPS_NT, smem) != cudaSuccess ||
+                per_sm < 1) {
+                (void)cudaGetLastError();
+                break;
+            }
+            int64_t cgrid = (int64_t)per_sm * num_sms();
+            if (cgrid > CPS_MAX_BLOCKS) cgrid = CPS_MAX_BLOCKS;
+            if (nb < cgrid) cgrid = nb;
+            if (cgrid * CPS_NT * spt < m) continue;          // more samples per thread needed
+            void* args[] = {(void*)&A, (void*)&spt};
+            if (cudaLaunchCooperativeKernel((void*)cps_ball_fused_kernel<R>, dim3((unsigned)cgrid), dim3(CPS_NT), args, smem, s) ==
+                cudaSuccess)
+                return check_launch(what);
+            (void)cudaGetLastError();          // cooperative launch not possible here: fall through to the two passes
+            break;
+        }
+    }
     cps_ball_norm_kernel<R><<<grid, CPS_NT, 0, s>>>(A);
     cps_ball_apply_kernel<R><<<grid, CPS_NT, 0, s>>>(A);
     return check_launch(what);
