@@ -40,6 +40,12 @@ PCS_DECL_REAL(pcs_prox_l1, (void* out, const void* x, double tau, int64_t n, voi
 PCS_DECL_REAL(pcs_proj_nonneg, (void* out, const void* x, int64_t n, void* stream))
 /* proj_segment (math/prox.py:340-343), Segment.prox (func/penalty.py:615-668); also proj_linfty_ball */
 PCS_DECL_REAL(pcs_proj_segment, (void* out, const void* x, double a, double b, int64_t n, void* stream))
+/* LogBarrier.prox (x + sqrt(x^2 + 4 tau))/2 (func/penalty.py:824-840); ShannonEntropy.prox tau W(exp(x/tau - 1)/tau)
+ * with the Lambert function evaluated in the log domain (func/penalty.py:905-922 -> scipy.special.lambertw);
+ * KLDivergence.prox (x - tau + sqrt((x - tau)^2 + 4 tau data))/2 (func/loss.py:666-682) */
+PCS_DECL_REAL(pcs_prox_logbarrier, (void* out, const void* x, double tau, int64_t n, void* stream))
+PCS_DECL_REAL(pcs_prox_shannon, (void* out, const void* x, double tau, int64_t n, void* stream))
+PCS_DECL_REAL(pcs_prox_kl, (void* out, const void* x, const void* data, double tau, int64_t n, void* stream))
 /* L21Norm.prox (func/penalty.py:551-557) for groups = tile(arange(n_groups), n_comp); is_complex: interleaved re/im */
 PCS_DECL_REAL(pcs_prox_l21, (void* out, const void* x, double tau, int64_t n_groups, int n_comp, int is_complex,
                              void* stream))
@@ -60,6 +66,11 @@ PCS_DECL_REAL(pcs_reduce_diffsumsq, (const void* x, const void* y, int64_t n, vo
                                      void* stream))
 PCS_DECL_REAL(pcs_reduce_dot, (const void* x, const void* y, int64_t n, void* out_f64, void* workspace, void* stream))
 PCS_DECL_REAL(pcs_reduce_minmax, (const void* x, int64_t n, void* out2_f64, void* workspace, void* stream))
+/* LogBarrier / ShannonEntropy / KLDivergence values (func/penalty.py:819-822, 899-903; func/loss.py:659-664): +inf
+ * outside the domain */
+PCS_DECL_REAL(pcs_reduce_neglog, (const void* x, int64_t n, void* out_f64, void* workspace, void* stream))
+PCS_DECL_REAL(pcs_reduce_xlogx, (const void* x, int64_t n, void* out_f64, void* workspace, void* stream))
+PCS_DECL_REAL(pcs_reduce_kl, (const void* x, const void* data, int64_t n, void* out_f64, void* workspace, void* stream))
 /* L21Norm.__call__ (func/penalty.py:548-549) */
 PCS_DECL_REAL(pcs_reduce_sumgroupnorm, (const void* x, int64_t n_groups, int n_comp, int is_complex, void* out_f64,
                                         void* workspace, void* stream))

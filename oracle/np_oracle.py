@@ -581,3 +581,55 @@ def power_iteration_lipschitz(op, n_iter=200, seed=0):
             return 0.0
         v = w / s
     return float(np.sqrt(s))
+
+
+class LogBarrier(Prox):
+    """func/penalty.py:776-840."""
+
+    def __init__(self, dim):
+        self.dim = dim
+
+    def __call__(self, x):
+        x = np.asarray(x, dtype=float)
+        y = 0 * x - np.inf
+        y[x > 0] = np.log(x[x > 0])
+        return -y.sum()
+
+    def prox(self, x, tau):
+        return (x + np.sqrt(x ** 2 + 4 * tau)) / 2
+
+
+class ShannonEntropy(Prox):
+    """func/penalty.py:843-922."""
+
+    def __init__(self, dim):
+        self.dim = dim
+
+    def __call__(self, x):
+        x = np.asarray(x, dtype=float)
+        y = 0 * x + np.inf
+        y[x == 0] = 0
+        y[x > 0] = x[x > 0] * np.log(x[x > 0])
+        return y.sum()
+
+    def prox(self, x, tau):
+        from scipy.special import lambertw
+        return np.real(tau * lambertw(np.exp(-1 + (x / tau)) / tau, k=0))
+
+
+class KLDivergence(Prox):
+    """func/loss.py:597-682."""
+
+    def __init__(self, dim, data):
+        self.dim, self.data = dim, np.asarray(data, dtype=float)
+
+    def __call__(self, x):
+        x = np.asarray(x, dtype=float)
+        z = 0 * x + np.inf
+        m = (x > 0) * (self.data > 0)
+        z[m] = self.data[m] * np.log(self.data[m] / x[m])
+        z[(x == 0) * (self.data >= 0)] = 0
+        return np.sum(z - self.data + x)
+
+    def prox(self, x, tau):
+        return (x - tau + np.sqrt((x - tau) ** 2 + 4 * tau * self.data)) / 2

@@ -98,6 +98,50 @@ def prox_l1(out, x, tau):
     return out
 
 
+def _real_only(x, what):
+    if x.is_complex():
+        raise NotImplementedError(f'{what} is defined for real vectors')
+
+
+def prox_logbarrier(out, x, tau):
+    _chk(out, x); _real_only(x, 'LogBarrier.prox')
+    _lib.call('pcs_prox_logbarrier' + sfx(x), ptr(out), ptr(x), float(tau), x.numel(), stream())
+    return out
+
+
+def prox_shannon(out, x, tau):
+    _chk(out, x); _real_only(x, 'ShannonEntropy.prox')
+    _lib.call('pcs_prox_shannon' + sfx(x), ptr(out), ptr(x), float(tau), x.numel(), stream())
+    return out
+
+
+def prox_kl(out, x, data, tau):
+    _chk(out, x, data); _real_only(x, 'KLDivergence.prox')
+    _lib.call('pcs_prox_kl' + sfx(x), ptr(out), ptr(x), ptr(data), float(tau), x.numel(), stream())
+    return out
+
+
+def reduce_neglog(x):
+    _chk(x); _real_only(x, 'LogBarrier')
+    out = _red_out(x)
+    _lib.call('pcs_reduce_neglog' + sfx(x), ptr(x), x.numel(), ptr(out), ptr(reduce_ws(x.device)), stream())
+    return out
+
+
+def reduce_xlogx(x):
+    _chk(x); _real_only(x, 'ShannonEntropy')
+    out = _red_out(x)
+    _lib.call('pcs_reduce_xlogx' + sfx(x), ptr(x), x.numel(), ptr(out), ptr(reduce_ws(x.device)), stream())
+    return out
+
+
+def reduce_kl(x, data):
+    _chk(x, data); _real_only(x, 'KLDivergence')
+    out = _red_out(x)
+    _lib.call('pcs_reduce_kl' + sfx(x), ptr(x), ptr(data), x.numel(), ptr(out), ptr(reduce_ws(x.device)), stream())
+    return out
+
+
 def proj_nonneg(out, x):
     _chk(out, x)
     _lib.call('pcs_proj_nonneg' + sfx(x), ptr(out), ptr(x), x.numel(), stream())

@@ -25,6 +25,12 @@ REAL = {
     'pcs_mul': [P, P, P, I64, P],
     'pcs_prox_l1': [P, P, F64, I64, P],
     'pcs_proj_nonneg': [P, P, I64, P],
+    'pcs_prox_logbarrier': [P, P, F64, I64, P],
+    'pcs_prox_shannon': [P, P, F64, I64, P],
+    'pcs_prox_kl': [P, P, P, F64, I64, P],
+    'pcs_reduce_neglog': [P, I64, P, P, P],
+    'pcs_reduce_xlogx': [P, I64, P, P, P],
+    'pcs_reduce_kl': [P, P, I64, P, P, P],
     'pcs_proj_segment': [P, P, F64, F64, I64, P],
     'pcs_prox_l21': [P, P, F64, I64, I32, I32, P],
     'pcs_reduce_sumsq': [P, I64, P, P, P],

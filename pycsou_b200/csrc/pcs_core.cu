@@ -60,7 +60,30 @@ enum EwOp {
     EW_NONNEG,      // out = max(x,0)
     EW_SEGMENT,     // out = clip(x,a,b)
     EW_SCALE_DEV,   // out = x * s[0]  (device scalar; used by l2 prox / l2-ball projection)
+    EW_PROX_LOGBARRIER,   // out = (x + sqrt(x^2 + 4a)) / 2
+    EW_PROX_KL,           // out = (x - a + sqrt((x - a)^2 + 4 a y)) / 2
+    EW_PROX_SHANNON,      // out = a * W(exp(x/a - 1) / a), W = principal branch of the Lambert function
 };
+
+// a * W(exp(x/a - 1)/a) evaluated in the log domain (no overflow for large x/a): w solves w + log w = L with
+// L = x/a - 1 - log a; Newton on that equation, w <- w (1 + L - log w) / (1 + w), converges quadratically from
+// w0 = L - log L (L > 1) or exp(L) / (1 + exp(L)) (else); 12 steps reach double precision from either start.
+template <typename T> __device__ __forceinline__ T lambert_scaled(T x, T a) {
+    const double L = (double)x / (double)a - 1.0 - log((double)a);
+    double w;
+    if (L > 1.0) w = L - log(L);
+    else { const double e = exp(L); w = e / (1.0 + e); }
+    if (!(w > 0.0)) return T(0);                       // exp(L) underflowed: W(z) ~ z = 0
+#pragma unroll 1
+    for (int it = 0; it < 12; ++it) {
+        const double wn = w * (1.0 + L - log(w)) / (1.0 + w);
+        if (!(wn > 0.0)) break;
+        const bool done = fabs(wn - w) <= 1e-16 * wn;
+        w = wn;
+        if (done) break;
+    }
+    return (T)((double)a * w);
+}
 
 template <typename T, int OP>
 __device__ __forceinline__ T ew_apply(T x, T y, T z, T a, T b, T c) {
@@ -71,6 +94,9 @@ __device__ __forceinline__ T ew_apply(T x, T y, T z, T a, T b, T c) {
     if (OP == EW_PROX_L1) return prox_l1<T>(x, a);
     if (OP == EW_NONNEG) return x < T(0) ? T(0) : x;
     if (OP == EW_SEGMENT) { T v = x < a ? a : x; return v > b ? b : v; }
+    if (OP == EW_PROX_LOGBARRIER) return (x + tsqrt<T>(x * x + T(4) * a)) / T(2);
+    if (OP == EW_PROX_KL) { const T d = x - a; return (d + tsqrt<T>(d * d + T(4) * a * y)) / T(2); }
+    if (OP == EW_PROX_SHANNON) return lambert_scaled<T>(x, a);
     return x;
 }
 
@@ -145,6 +171,26 @@ template <typename T> static int pcs_mul_impl(T* out, const T* x, const T* y, in
 PCS_EXPORT_REAL(pcs_mul, (void* out, const void* x, const void* y, int64_t n, void* stream),
                 ((T*)out, (const T*)x, (const T*)y, n, (cudaStream_t)stream))
 
+// LogBarrier.prox (func/penalty.py:824-840), ShannonEntropy.prox (:905-922), KLDivergence.prox (func/loss.py:666-682)
+template <typename T> static int pcs_prox_logbarrier_impl(T* out, const T* x, T tau, int64_t n, cudaStream_t s) {
+    PCS_REQUIRE(tau > T(0), "pcs_prox_logbarrier: tau must be positive");
+    return ew_launch<T, EW_PROX_LOGBARRIER, 1>(out, x, nullptr, nullptr, tau, T(0), T(0), n, s, "pcs_prox_logbarrier");
+}
+PCS_EXPORT_REAL(pcs_prox_logbarrier, (void* out, const void* x, double tau, int64_t n, void* stream),
+                ((T*)out, (const T*)x, (T)tau, n, (cudaStream_t)stream))
+template <typename T> static int pcs_prox_shannon_impl(T* out, const T* x, T tau, int64_t n, cudaStream_t s) {
+    PCS_REQUIRE(tau > T(0), "pcs_prox_shannon: tau must be positive");
+    return ew_launch<T, EW_PROX_SHANNON, 1>(out, x, nullptr, nullptr, tau, T(0), T(0), n, s, "pcs_prox_shannon");
+}
+PCS_EXPORT_REAL(pcs_prox_shannon, (void* out, const void* x, double tau, int64_t n, void* stream),
+                ((T*)out, (const T*)x, (T)tau, n, (cudaStream_t)stream))
+template <typename T> static int pcs_prox_kl_impl(T* out, const T* x, const T* data, T tau, int64_t n, cudaStream_t s) {
+    PCS_REQUIRE(tau > T(0), "pcs_prox_kl: tau must be positive");
+    return ew_launch<T, EW_PROX_KL, 2>(out, x, data, nullptr, tau, T(0), T(0), n, s, "pcs_prox_kl");
+}
+PCS_EXPORT_REAL(pcs_prox_kl, (void* out, const void* x, const void* data, double tau, int64_t n, void* stream),
+                ((T*)out, (const T*)x, (const T*)data, (T)tau, n, (cudaStream_t)stream))
+
 // L1Norm.prox (func/penalty.py:194-245 via func/base.py:239-240)
 template <typename T> static int pcs_prox_l1_impl(T* out, const T* x, T tau, int64_t n, cudaStream_t s) {
     return ew_launch<T, EW_PROX_L1, 1>(out, x, nullptr, nullptr, tau, T(0), T(0), n, s, "pcs_prox_l1");
@@ -213,7 +259,7 @@ PCS_EXPORT_REAL(pcs_prox_l21,
 constexpr int RD_BLOCK = 256;
 constexpr int RD_CTAS_PER_SM = 4;
 
-enum RdOp { RD_SUMSQ, RD_DIFFSUMSQ, RD_SUMABS, RD_DOT, RD_MIN, RD_MAX };
+enum RdOp { RD_SUMSQ, RD_DIFFSUMSQ, RD_SUMABS, RD_DOT, RD_MIN, RD_MAX, RD_NEGLOG, RD_XLOGX, RD_KL };
 
 // Workspace layout (doubles): [0 .. 4*max_blocks) partials, then one 8-byte ticket slot.
 extern "C" int64_t pcs_reduce_workspace_bytes(void) {
@@ -233,6 +279,13 @@ __global__ void __launch_bounds__(RD_BLOCK) reduce_kernel(const T* __restrict__ 
         if (OP == RD_DIFFSUMSQ) { double d = a - (double)y[i]; acc[0] += d * d; }
         if (OP == RD_SUMABS) acc[0] += fabs(a);
         if (OP == RD_DOT) acc[0] += a * (double)y[i];
+        if (OP == RD_NEGLOG) acc[0] += a > 0.0 ? -log(a) : INFINITY;                       // func/penalty.py:819-822
+        if (OP == RD_XLOGX) acc[0] += a > 0.0 ? a * log(a) : (a == 0.0 ? 0.0 : INFINITY);  // func/penalty.py:899-903
+        if (OP == RD_KL) {                                                                 // func/loss.py:659-664
+            const double d = (double)y[i];
+            const double z = (a > 0.0 && d > 0.0) ? d * log(d / a) : ((a == 0.0 && d >= 0.0) ? 0.0 : INFINITY);
+            acc[0] += z - d + a;
+        }
     }
     grid_sum_finish<1, RD_BLOCK>(acc, partials, ticket, out, sm);
 }
@@ -240,7 +293,7 @@ __global__ void __launch_bounds__(RD_BLOCK) reduce_kernel(const T* __restrict__ 
 template <typename T, int OP>
 static int reduce_launch(const T* x, const T* y, int64_t n, double* out, void* ws, cudaStream_t s, const char* what) {
     PCS_REQUIRE(n >= 0 && out && ws, "%s: bad arguments", what);
-    PCS_REQUIRE(n == 0 || (x && (OP != RD_DIFFSUMSQ && OP != RD_DOT || y)), "%s: null pointer", what);
+    PCS_REQUIRE(n == 0 || (x && ((OP != RD_DIFFSUMSQ && OP != RD_DOT && OP != RD_KL) || y)), "%s: null pointer", what);
     int grid = grid_for(n, RD_BLOCK, RD_CTAS_PER_SM);
     double* partials = (double*)ws;
     unsigned int* ticket = (unsigned int*)(partials + 4 * (int64_t)pcs::num_sms() * 8);
@@ -266,6 +319,9 @@ PCS_REDUCE1(pcs_reduce_sumsq, RD_SUMSQ)          // ||x||^2           (np.linalg
 PCS_REDUCE1(pcs_reduce_sumabs, RD_SUMABS)        // sum |x|           (L1Norm.__call__, func/penalty.py:240-241)
 PCS_REDUCE2(pcs_reduce_diffsumsq, RD_DIFFSUMSQ)  // ||x - y||^2
 PCS_REDUCE2(pcs_reduce_dot, RD_DOT)              // <x, y>
+PCS_REDUCE1(pcs_reduce_neglog, RD_NEGLOG)        // -sum log x (inf unless x > 0)            LogBarrier.__call__
+PCS_REDUCE1(pcs_reduce_xlogx, RD_XLOGX)          // sum x log x (0 at 0, inf below)          ShannonEntropy.__call__
+PCS_REDUCE2(pcs_reduce_kl, RD_KL)                // sum y log(y/x) - y + x                   KLDivergence.__call__
 
 // min and max in one pass (IndicatorFunctional.__call__ conditions, func/penalty.py:610,666)
 template <typename T>

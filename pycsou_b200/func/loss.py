@@ -11,6 +11,8 @@ from numbers import Number
 import numpy as np
 import torch
 
+from .. import _kernels as K
+from .._array import to_device
 from ..core.functional import DifferentiableFunctional, ProxFuncPreComp, ProximableFunctional
 from .base import IndicatorFunctional
 from .penalty import L1Norm, L2Ball, L2Norm, LInftyBall, SquaredL2Norm
@@ -69,4 +71,27 @@ SquaredL1Loss = _out_of_scope('SquaredL1Loss')
 L1BallLoss = _out_of_scope('L1BallLoss')
 LInftyLoss = _out_of_scope('LInftyLoss')
 ConsistencyLoss = _out_of_scope('ConsistencyLoss')
-KLDivergence = _out_of_scope('KLDivergence')
+
+
+class KLDivergence(ProximableFunctional):
+    r"""Generalised Kullback-Leibler divergence :math:`\sum_i y_i\log(y_i/x_i) - y_i + x_i` (reference
+    ``func/loss.py:597-682``); prox ``(x - tau + sqrt((x - tau)^2 + 4 tau y)) / 2``.  ``data`` is uploaded once."""
+
+    def __init__(self, dim: int, data):
+        super(KLDivergence, self).__init__(dim=dim, data=None, is_differentiable=False, is_linear=False)
+        self.data = data
+        self._data_dev = None
+
+    def _d(self, x):
+        if self._data_dev is None or self._data_dev.dtype != x.dtype or self._data_dev.device != x.device:
+            d = self.data
+            if isinstance(d, Number):
+                d = np.full(self.dim, d)
+            self._data_dev = to_device(d, x.dtype)
+        return self._data_dev
+
+    def _apply(self, x):
+        return float(K.reduce_kl(x, self._d(x)).item())
+
+    def _prox(self, x, tau):
+        return K.prox_kl(torch.empty_like(x), x, self._d(x), tau)

@@ -216,6 +216,34 @@ L1Ball = _out_of_scope('L1Ball')
 LInftyNorm = _out_of_scope('LInftyNorm')
 RealLine = _out_of_scope('RealLine')
 ImagLine = _out_of_scope('ImagLine')
-LogBarrier = _out_of_scope('LogBarrier')
-ShannonEntropy = _out_of_scope('ShannonEntropy')
+
+
+class LogBarrier(ProximableFunctional):
+    r""":math:`-\sum_i \log x_i` (``+inf`` unless ``x > 0``); prox ``(x + sqrt(x^2 + 4 tau)) / 2``
+    (reference ``func/penalty.py:776-840``)."""
+
+    def __init__(self, dim: int):
+        super(LogBarrier, self).__init__(dim=dim, data=None, is_differentiable=False, is_linear=False)
+
+    def _apply(self, x):
+        return float(K.reduce_neglog(x).item())
+
+    def _prox(self, x, tau):
+        return K.prox_logbarrier(torch.empty_like(x), x, tau)
+
+
+class ShannonEntropy(ProximableFunctional):
+    r""":math:`\sum_i x_i \log x_i` (``0`` at 0, ``+inf`` below); prox ``tau W(exp(x/tau - 1)/tau)`` with the principal
+    Lambert function (reference ``func/penalty.py:843-922``)."""
+
+    def __init__(self, dim: int):
+        super(ShannonEntropy, self).__init__(dim=dim, data=None, is_differentiable=False, is_linear=False)
+
+    def _apply(self, x):
+        return float(K.reduce_xlogx(x).item())
+
+    def _prox(self, x, tau):
+        return K.prox_shannon(torch.empty_like(x), x, tau)
+
+
 QuadraticForm = _out_of_scope('QuadraticForm')

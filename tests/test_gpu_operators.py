@@ -282,3 +282,41 @@ def test_moving_average_operators():
     # constant signal: the interior is reproduced exactly (the window sums to one)
     y = MovingAverage1D(5, (50,))(np.ones(50))
     assert np.allclose(y[2:-2], 1.0) and y[0] < 1.0
+
+
+@pytest.mark.parametrize('dtype,tol', [('float64', 1e-12), ('float32', 2e-6)])
+def test_entropy_and_barrier_functionals(dtype, tol):
+    """LogBarrier / ShannonEntropy / KLDivergence (reference func/penalty.py:776-922, func/loss.py:597-682): the
+    reference's doctest literals, values incl. the +inf cases, proxes against the oracle (scipy's Lambert W)."""
+    from pycsou_b200.func.loss import KLDivergence
+    from pycsou_b200.func.penalty import LogBarrier, ShannonEntropy
+    x1 = np.arange(10).astype(dtype)
+    f, fo = LogBarrier(10), O.LogBarrier(10)
+    assert f(x1) == np.inf and np.isclose(f(x1 + 2), -17.502307845873887, rtol=tol * 10)
+    assert np.array_equal(np.round(f.prox(x1, tau=1)), [1, 2, 2, 3, 4, 5, 6, 7, 8, 9])
+    g, go = ShannonEntropy(10), O.ShannonEntropy(10)
+    x2 = np.zeros(10, dtype=dtype)
+    x2[0] = 10
+    assert np.isclose(g(x1), 79.05697962199447, rtol=tol * 10) and np.isclose(g(x2), 23.02585092994046, rtol=tol * 10)
+    assert g(x1 - 1) == np.inf
+    assert np.array_equal(np.round(g.prox(x1, tau=2)), [0, 0, 1, 1, 1, 2, 2, 3, 3, 4])
+    y = np.arange(10).astype(dtype)
+    k, ko = KLDivergence(10, y), O.KLDivergence(10, y)
+    assert np.isclose(k(2 * y), 13.80837687480246, rtol=tol * 10)
+    assert k(y - 1) == np.inf
+    assert np.array_equal(np.round(k.prox(2 * y, tau=1)), [0, 2, 4, 6, 8, 10, 12, 14, 16, 18])
+    r = rng(12)
+    n = 20000
+    x = (r.standard_normal(n) * 5).astype(dtype)
+    d = r.random(n).astype(dtype) * 3
+    for tau in (0.05, 1.0, 7.5):
+        assert rel_l2(f.__class__(n).prox(x, tau), O.LogBarrier(n).prox(x.astype(np.float64), tau)) < tol
+        assert rel_l2(KLDivergence(n, d).prox(x, tau), O.KLDivergence(n, d.astype(np.float64)).prox(x.astype(np.float64), tau)) < tol
+        assert rel_l2(ShannonEntropy(n).prox(x, tau), O.ShannonEntropy(n).prox(x.astype(np.float64), tau)) < 20 * tol
+    xp = np.abs(x) + 0.1
+    assert np.isclose(LogBarrier(n)(xp), O.LogBarrier(n)(xp.astype(np.float64)), rtol=10 * tol)
+    assert np.isclose(ShannonEntropy(n)(xp), O.ShannonEntropy(n)(xp.astype(np.float64)), rtol=10 * tol)
+    assert np.isclose(KLDivergence(n, d)(xp), O.KLDivergence(n, d.astype(np.float64))(xp.astype(np.float64)), rtol=10 * tol)
+    # Moreau identity through the base class (core/functional.py:207) and the solver-facing scaling 2 * f
+    z = np.abs(x[:100]) + 0.5
+    assert rel_l2((2 * LogBarrier(100)).fenchel_prox(z, 0.7), (2 * O.LogBarrier(100)).fenchel_prox(z.astype(np.float64), 0.7)) < 10 * tol

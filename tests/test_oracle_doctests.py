@@ -158,3 +158,19 @@ def test_squared_l2_loss_gradient():
     F = O.HalfSquaredL2Loss(y, Gop, G_lipschitz=1.5)
     assert np.allclose(F.gradient(x), Gop.rmatvec(Gop.matvec(x) - y))
     assert np.isclose(F.diff_lipschitz_cst, 1.5 ** 2)
+
+
+def test_entropy_and_barrier_functionals():
+    # func/penalty.py:793-798 (LogBarrier), :867-872 (ShannonEntropy); func/loss.py:632-638 (KLDivergence)
+    x1 = np.arange(10)
+    f = O.LogBarrier(10)
+    assert f(x1) == np.inf and f(x1 + 2) == -17.502307845873887
+    assert np.array_equal(np.round(f.prox(x1, tau=1)), [1, 2, 2, 3, 4, 5, 6, 7, 8, 9])
+    g = O.ShannonEntropy(10)
+    x2 = np.zeros(10)
+    x2[0] = 10
+    assert g(x1) == 79.05697962199447 and g(x2) == 23.02585092994046
+    assert np.array_equal(np.round(g.prox(x1, tau=2)), [0, 0, 1, 1, 1, 2, 2, 3, 3, 4])
+    k = O.KLDivergence(10, np.arange(10))
+    assert k(2 * np.arange(10)) == 13.80837687480246
+    assert np.array_equal(np.round(k.prox(2 * np.arange(10), tau=1)), [0, 2, 4, 6, 8, 10, 12, 14, 16, 18])

@@ -66,3 +66,17 @@ def test_step_size_rule_matches_reference(ref):
     assert (s.tau, s.sigma, s.rho) == O.pds_step_sizes(0, 1.7)
     s = PDS(dim=30, F=SquaredL2Loss(dim=30, data=np.ones(30)), verbose=None)
     assert (s.tau, s.sigma, s.rho) == O.pds_step_sizes(2, 0, has_H=False)
+
+
+def test_entropy_and_barrier_match_reference(ref):
+    from pycsou.func import penalty as P, loss as L
+    rng = np.random.default_rng(2)
+    x, d = 4 * rng.standard_normal(50), 3 * rng.random(50)
+    xp = np.abs(x) + 0.1
+    for tau in (0.05, 0.7, 3.0):
+        assert np.array_equal(P.LogBarrier(50).prox(x.copy(), tau), O.LogBarrier(50).prox(x, tau))
+        assert np.array_equal(P.ShannonEntropy(50).prox(x.copy(), tau), O.ShannonEntropy(50).prox(x, tau))
+        assert np.array_equal(L.KLDivergence(50, d).prox(x.copy(), tau), O.KLDivergence(50, d).prox(x, tau))
+    assert P.LogBarrier(50)(xp) == O.LogBarrier(50)(xp) and P.LogBarrier(50)(x) == O.LogBarrier(50)(x) == np.inf
+    assert P.ShannonEntropy(50)(xp) == O.ShannonEntropy(50)(xp)
+    assert L.KLDivergence(50, d)(xp) == O.KLDivergence(50, d)(xp)
