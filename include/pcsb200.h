@@ -85,6 +85,10 @@ PCS_DECL_REAL(pcs_secondderiv_fwd, (void* out, const void* x, int64_t outer, int
                                     int edge, double step, int accumulate, void* stream))
 PCS_DECL_REAL(pcs_secondderiv_adj, (void* out, const void* x, int64_t outer, int64_t n, int64_t inner, int kind,
                                     int edge, double step, int accumulate, void* stream))
+/* Integration1D = pylops CausalIntegration(halfcurrent=False) (linop/diff.py:1071-1137): forward
+ * y[i] = step * sum_{j<=i} x[j] along the axis, adjoint y[i] = step * sum_{j>=i} x[j] */
+PCS_DECL_REAL(pcs_cumsum_fwd, (void* out, const void* x, int64_t outer, int64_t n, int64_t inner, double step, void* stream))
+PCS_DECL_REAL(pcs_cumsum_adj, (void* out, const void* x, int64_t outer, int64_t n, int64_t inner, double step, void* stream))
 /* 2-D Gradient: out = [d/daxis0 ; d/daxis1] (2*H*W); adjoint: out (H*W) from z (2*H*W) */
 PCS_DECL_REAL(pcs_grad2d_fwd, (void* out, const void* x, int64_t H, int64_t W, int kind, int edge, double step0,
                                double step1, void* stream))

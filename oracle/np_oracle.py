@@ -633,3 +633,75 @@ class KLDivergence(Prox):
 
     def prox(self, x, tau):
         return (x - tau + np.sqrt((x - tau) ** 2 + 4 * tau * self.data)) / 2
+
+
+class QuadraticForm:
+    """func/penalty.py:925-990: x^T Q x, gradient 2 Q x (Q = identity when linop is None)."""
+
+    def __init__(self, dim, linop=None):
+        self.dim, self.linop = dim, linop
+        self.diff_lipschitz_cst = 2 if linop is None else 2 * linop.diff_lipschitz_cst
+
+    def __call__(self, x):
+        return np.dot(x.conj(), x if self.linop is None else self.linop.matvec(x))
+
+    def gradient(self, x):
+        return 2 * x if self.linop is None else 2 * self.linop.matvec(x)
+
+
+class FirstDirectionalDerivative:
+    """linop/diff.py:380-486 -> pylops.FirstDirectionalDerivative(dims, v, sampling, edge, dtype, kind)
+    = Sum(axis 0) * Diagonal(v) * Gradient: y = sum_i v_i * d_i x; adjoint = Gradient^T (v_i * y stacked)."""
+
+    def __init__(self, shape, directions, step=1., edge=True, dtype='float64', kind='centered'):
+        self.dims = tuple(shape)
+        self.N = int(np.prod(shape))
+        nd = len(self.dims)
+        v = np.asarray(directions, dtype=float)
+        self.v = np.repeat(v, self.N).reshape(nd, self.N) if v.ndim == 1 else v.reshape(nd, self.N)
+        self.G = pl.Gradient(dims=shape, sampling=step, edge=edge, dtype=dtype, kind=kind)
+        self.shape = (self.N, self.N)
+
+    def matvec(self, x):
+        return (self.v * self.G.matvec(x).reshape(len(self.dims), self.N)).sum(axis=0)
+
+    def rmatvec(self, y):
+        return self.G.rmatvec((self.v * y[None, :]).reshape(-1))
+
+
+class SecondDirectionalDerivative:
+    """linop/diff.py:489-606: KillEdge * pylops.SecondDirectionalDerivative, the latter being -D^T D with D the centered
+    first directional derivative; KillEdge zeroes the two outermost samples of every axis."""
+
+    def __init__(self, shape, directions, step=1., edge=True, dtype='float64'):
+        self.D = FirstDirectionalDerivative(shape, directions, step, edge, dtype, 'centered')
+        kill = np.ones(shape)
+        for axis in range(len(shape)):
+            kill = np.swapaxes(kill, axis, 0)
+            kill[-2:] = 0
+            kill[:2] = 0
+            kill = np.swapaxes(kill, 0, axis)
+        self.kill = kill.reshape(-1)
+        self.shape = self.D.shape
+
+    def matvec(self, x):
+        return self.kill * (-self.D.rmatvec(self.D.matvec(x)))
+
+    def rmatvec(self, z):
+        return -self.D.rmatvec(self.D.matvec(self.kill * z))
+
+
+class Integration1D:
+    """linop/diff.py:1071-1137 -> pylops.CausalIntegration(N, dims, dir, sampling, halfcurrent=False):
+    matvec = sampling * cumsum along the axis; rmatvec = sampling * reversed cumsum (flip, cumsum, flip)."""
+
+    def __init__(self, size, shape=None, axis=0, step=1., dtype='float64'):
+        self.dims = (size,) if shape is None else tuple(shape)
+        self.axis, self.step, self.shape = axis, step, (size, size)
+
+    def matvec(self, x):
+        return (self.step * np.cumsum(x.reshape(self.dims), axis=self.axis)).reshape(-1)
+
+    def rmatvec(self, y):
+        Y = np.flip(y.reshape(self.dims), axis=self.axis)
+        return (self.step * np.flip(np.cumsum(Y, axis=self.axis), axis=self.axis)).reshape(-1)

@@ -239,6 +239,16 @@ def firstderiv(out, x, outer, n, inner, kind, edge, step, adjoint=False, accumul
     return out
 
 
+def cumsum(out, x, outer, n, inner, step, adjoint=False):
+    """Running sum along one axis times ``step`` (forward) / the same from the far end (adjoint)."""
+    _chk(out, x)
+    e = 2 if x.is_complex() else 1
+    name = 'pcs_cumsum_adj' if adjoint else 'pcs_cumsum_fwd'
+    _lib.call(name + sfx(x), ptr(real_view(out)), ptr(real_view(x)), int(outer), int(n), int(inner) * e, float(step),
+              stream())
+    return out
+
+
 def secondderiv(out, x, outer, n, inner, edge, step, adjoint=False, accumulate=False):
     _chk(out, x)
     e = 2 if x.is_complex() else 1

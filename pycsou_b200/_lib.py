@@ -46,6 +46,8 @@ REAL = {
     'pcs_firstderiv_adj': [P, P, I64, I64, I64, I32, I32, F64, I32, P],
     'pcs_secondderiv_fwd': [P, P, I64, I64, I64, I32, I32, F64, I32, P],
     'pcs_secondderiv_adj': [P, P, I64, I64, I64, I32, I32, F64, I32, P],
+    'pcs_cumsum_fwd': [P, P, I64, I64, I64, F64, P],
+    'pcs_cumsum_adj': [P, P, I64, I64, I64, F64, P],
     'pcs_grad2d_fwd': [P, P, I64, I64, I32, I32, F64, F64, P],
     'pcs_grad2d_adj': [P, P, I64, I64, I32, I32, F64, F64, P],
     'pcs_laplacian2d_fwd': [P, P, I64, I64, F64, F64, F64, F64, I32, P],

@@ -180,3 +180,91 @@ static int pcs_laplacian2d_adj_impl(T* o, const T* x, int64_t H, int64_t W, doub
     return lap2d_launch<T, true>(o, x, H, W, w0, w1, s0, s1, e, s, "pcs_laplacian2d_adj");
 }
 PCS_EXPORT_REAL(pcs_laplacian2d_adj, LAP_PARAMS, LAP_ARGS)
+
+// ---- Integration1D: pylops CausalIntegration(halfcurrent=False) behind pycsou/linop/diff.py:1071-1137 ------------------
+// forward y[i] = step * sum_{j <= i} x[j] along the axis; adjoint y[i] = step * sum_{j >= i} x[j] (the scan run backwards).
+// Lines with inner > 1 (the axis is not the fastest one): one thread per line, coalesced across `inner`.  Contiguous
+// lines (inner == 1): one block per line, chunks of 1024 samples scanned with warp shuffles and a running carry.
+namespace {
+template <typename T, bool REV>
+__global__ void __launch_bounds__(256) cumsum_strided_kernel(T* __restrict__ out, const T* __restrict__ x, int64_t outer,
+                                                             int64_t n, int64_t inner, T step) {
+    const int64_t lines = outer * inner;
+    for (int64_t l = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; l < lines; l += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t o = l / inner, i = l - o * inner;
+        const int64_t base = o * n * inner + i;
+        T acc = T(0);
+        for (int64_t k = 0; k < n; ++k) {
+            const int64_t kk = REV ? n - 1 - k : k;
+            acc += x[base + kk * inner];
+            out[base + kk * inner] = step * acc;
+        }
+    }
+}
+template <typename T, bool REV>
+__global__ void __launch_bounds__(256) cumsum_line_kernel(T* __restrict__ out, const T* __restrict__ x, int64_t n, T step) {
+    constexpr int ITEMS = 4, NT = 256, CHUNK = ITEMS * NT;
+    __shared__ T warp_tot[NT / 32];
+    __shared__ T s_carry;
+    const T* xl = x + (int64_t)blockIdx.x * n;
+    T* ol = out + (int64_t)blockIdx.x * n;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_carry = T(0);
+    __syncthreads();
+    for (int64_t c0 = 0; c0 < n; c0 += CHUNK) {
+        T v[ITEMS];
+        T run = T(0);
+#pragma unroll
+        for (int e = 0; e < ITEMS; ++e) {
+            const int64_t k = c0 + (int64_t)tid * ITEMS + e;
+            const T xv = k < n ? xl[REV ? n - 1 - k : k] : T(0);
+            run += xv;
+            v[e] = run;
+        }
+        T incl = run;                                             // inclusive scan of the thread totals inside the warp
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const T t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) warp_tot[warp] = incl;
+        __syncthreads();
+        T woff = T(0);
+        for (int w = 0; w < warp; ++w) woff += warp_tot[w];
+        const T carry = s_carry;
+        const T off = carry + woff + (incl - run);
+#pragma unroll
+        for (int e = 0; e < ITEMS; ++e) {
+            const int64_t k = c0 + (int64_t)tid * ITEMS + e;
+            if (k < n) ol[REV ? n - 1 - k : k] = step * (off + v[e]);
+        }
+        __syncthreads();
+        if (tid == NT - 1) s_carry = off + run;
+        __syncthreads();
+    }
+}
+template <typename T, bool REV>
+int cumsum_launch(T* out, const T* x, int64_t outer, int64_t n, int64_t inner, double step, cudaStream_t s, const char* what) {
+    PCS_REQUIRE(outer >= 0 && n >= 0 && inner >= 0 && outer < (1ll << 31), "%s: bad dimensions", what);
+    if (outer * n * inner == 0) return PCS_OK;
+    PCS_REQUIRE(out && x && out != x, "%s: null or aliased pointer", what);
+    if (inner == 1 && n >= 2048) {
+        cumsum_line_kernel<T, REV><<<(unsigned)outer, 256, 0, s>>>(out, x, n, (T)step);
+    } else {
+        const int64_t lines = outer * inner;
+        cumsum_strided_kernel<T, REV><<<grid_for(lines, 256, 8), 256, 0, s>>>(out, x, outer, n, inner, (T)step);
+    }
+    return check_launch(what);
+}
+}  // namespace
+#define CUMSUM_PARAMS (void* out, const void* x, int64_t outer, int64_t n, int64_t inner, double step, void* stream)
+template <typename T>
+static int pcs_cumsum_fwd_impl(T* o, const T* x, int64_t outer, int64_t n, int64_t inner, double step, cudaStream_t s) {
+    return cumsum_launch<T, false>(o, x, outer, n, inner, step, s, "pcs_cumsum_fwd");
+}
+PCS_EXPORT_REAL(pcs_cumsum_fwd, CUMSUM_PARAMS, ((T*)out, (const T*)x, outer, n, inner, step, (cudaStream_t)stream))
+template <typename T>
+static int pcs_cumsum_adj_impl(T* o, const T* x, int64_t outer, int64_t n, int64_t inner, double step, cudaStream_t s) {
+    return cumsum_launch<T, true>(o, x, outer, n, inner, step, s, "pcs_cumsum_adj");
+}
+PCS_EXPORT_REAL(pcs_cumsum_adj, CUMSUM_PARAMS, ((T*)out, (const T*)x, outer, n, inner, step, (cudaStream_t)stream))

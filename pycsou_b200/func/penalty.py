@@ -246,4 +246,22 @@ class ShannonEntropy(ProximableFunctional):
         return K.prox_shannon(torch.empty_like(x), x, tau)
 
 
-QuadraticForm = _out_of_scope('QuadraticForm')
+
+
+class QuadraticForm(DifferentiableFunctional):
+    r""":math:`x^T Q x` for a positive semi-definite operator ``Q`` (identity if ``None``), gradient :math:`2Qx`
+    (reference ``func/penalty.py:925-990``).  ``Q`` is any operator of this package; real vectors."""
+
+    def __init__(self, dim: int, linop=None):
+        self.linop = linop
+        beta = 2 if linop is None else 2 * linop.diff_lipschitz_cst
+        super(QuadraticForm, self).__init__(dim=dim, data=None, is_linear=False, diff_lipschitz_cst=beta)
+
+    def _apply(self, x):
+        if self.linop is None:
+            return float(K.sumsq(x).item())
+        return float(K.dot(x, self.linop._apply(x)).item())
+
+    def _jacobianT(self, x):
+        q = x if self.linop is None else self.linop._apply(x)
+        return K.scale(torch.empty_like(x), 2.0, q)

@@ -16,6 +16,7 @@ import numpy as np
 import torch
 
 from .. import _kernels as K
+from .._array import to_device
 from ..core.linop import LinearOperator
 
 __all__ = ['FirstDerivative', 'SecondDerivative', 'Gradient', 'Laplacian', 'GeneralisedDerivative',
@@ -169,9 +170,140 @@ def _out_of_scope(name):
 
 
 GeneralisedDerivative = _out_of_scope('GeneralisedDerivative')
-FirstDirectionalDerivative = _out_of_scope('FirstDirectionalDerivative')
-SecondDirectionalDerivative = _out_of_scope('SecondDirectionalDerivative')
-DirectionalGradient = _out_of_scope('DirectionalGradient')
-DirectionalLaplacian = _out_of_scope('DirectionalLaplacian')
+
+
+class FirstDirectionalDerivativeOperator(LinearOperator):
+    r""":math:`d_v x = \sum_i v_i\,\partial_i x` (pylops ``FirstDirectionalDerivative`` = ``Sum * Diagonal(v) * Gradient``):
+    the gradient kernels, one element-wise product with the direction field and a sum over the axes.  ``directions`` has
+    shape ``(ndim,)`` (one direction everywhere) or ``(ndim, *shape)`` (a direction per pixel)."""
+
+    def __init__(self, shape, directions, step, edge, dtype, kind):
+        self.array_shape = tuple(int(s) for s in shape)
+        nd, N = len(self.array_shape), int(np.prod(shape))
+        v = np.asarray(directions, dtype=np.float64)
+        if v.shape == (nd,):
+            v = np.repeat(v, N)
+        elif v.shape == (nd,) + self.array_shape:
+            v = v.reshape(-1)
+        else:
+            raise ValueError('directions must have shape (ndim,) or (ndim, *shape)')
+        self.directions, self.N, self.nd = v, N, nd
+        self.grad = GradientOperator(shape, step, edge, dtype, kind)
+        self._v = {}
+        super().__init__(shape=(N, N), dtype=np.dtype(dtype))
+
+    def _vdev(self, like):
+        key = (like.dtype, like.device)
+        if key not in self._v:
+            self._v[key] = to_device(self.directions, like.dtype)
+        return self._v[key]
+
+    def _apply(self, x):
+        if x.is_complex():
+            raise NotImplementedError('complex directional derivative')
+        g = self.grad._apply(x)
+        K.mul(g, g, self._vdev(x))
+        N = self.N
+        out = K.lincomb2(torch.empty_like(x), 1.0, g[:N], 1.0, g[N:2 * N]) if self.nd > 1 else g[:N].clone()
+        for ax in range(2, self.nd):
+            K.lincomb2(out, 1.0, out, 1.0, g[ax * N:(ax + 1) * N])
+        return out
+
+    def _adjoint(self, y):
+        if y.is_complex():
+            raise NotImplementedError('complex directional derivative')
+        v, N = self._vdev(y), self.N
+        t = torch.empty(self.nd * N, dtype=y.dtype, device=y.device)
+        for ax in range(self.nd):
+            K.mul(t[ax * N:(ax + 1) * N], v[ax * N:(ax + 1) * N], y)
+        return self.grad._adjoint(t)
+
+
+class SecondDirectionalDerivativeOperator(LinearOperator):
+    r""":math:`-d_v^T d_v` with the two outermost samples of every axis zeroed in the OUTPUT (pylops
+    ``SecondDirectionalDerivative`` followed by the reference's edge-killing ``DiagonalOperator``, ``diff.py:596-606``)."""
+
+    def __init__(self, shape, directions, step, edge, dtype):
+        self.first = FirstDirectionalDerivativeOperator(shape, directions, step, edge, dtype, 'centered')
+        kill = np.ones(shape)
+        for axis in range(len(shape)):
+            kill = np.swapaxes(kill, axis, 0)
+            kill[-2:] = 0
+            kill[:2] = 0
+            kill = np.swapaxes(kill, 0, axis)
+        self.kill_edges = kill.reshape(-1)
+        self._k = {}
+        N = self.first.N
+        super().__init__(shape=(N, N), dtype=np.dtype(dtype))
+
+    def _kdev(self, like):
+        key = (like.dtype, like.device)
+        if key not in self._k:
+            self._k[key] = to_device(self.kill_edges, like.dtype)
+        return self._k[key]
+
+    def _apply(self, x):
+        y = self.first._adjoint(self.first._apply(x))
+        K.mul(y, y, self._kdev(x))
+        return K.scale(y, -1.0, y)
+
+    def _adjoint(self, z):
+        t = K.mul(torch.empty_like(z), z, self._kdev(z))
+        y = self.first._adjoint(self.first._apply(t))
+        return K.scale(y, -1.0, y)
+
+
+def FirstDirectionalDerivative(shape: tuple, directions, step=1., edge: bool = True, dtype: str = 'float64',
+                               kind: str = 'centered') -> LinearOperator:
+    return FirstDirectionalDerivativeOperator(shape, directions, step, edge, dtype, kind)
+
+
+def SecondDirectionalDerivative(shape: tuple, directions, step=1., edge: bool = True,
+                                dtype: str = 'float64') -> LinearOperator:
+    return SecondDirectionalDerivativeOperator(shape, directions, step, edge, dtype)
+
+
+def DirectionalGradient(first_directional_derivatives) -> LinearOperator:
+    """Stack of first directional derivatives (reference ``diff.py:609-688``)."""
+    from .base import LinOpVStack
+    return LinOpVStack(*first_directional_derivatives)
+
+
+def DirectionalLaplacian(second_directional_derivatives, weights=None) -> LinearOperator:
+    """Weighted sum of second directional derivatives, exactly as the reference accumulates it (``diff.py:691-774``: the
+    first weight is not applied)."""
+    lap = second_directional_derivatives[0]
+    if weights is None:
+        weights = [1.] * len(second_directional_derivatives)
+    elif len(weights) != len(second_directional_derivatives):
+        raise ValueError('The number of weights and operators provided differ.')
+    for i in range(1, len(second_directional_derivatives)):
+        lap += weights[i] * second_directional_derivatives[i]
+    return lap
 GeneralisedLaplacian = _out_of_scope('GeneralisedLaplacian')
-Integration1D = _out_of_scope('Integration1D')
+
+
+class Integration1DOperator(LinearOperator):
+    r"""Causal integration ``y[i] = step * sum_{j<=i} x[j]`` along ``axis`` (reference ``diff.py:1071-1137`` ->
+    ``pylops.CausalIntegration(halfcurrent=False)``); the adjoint runs the sum from the far end."""
+
+    def __init__(self, size, shape, axis, step, dtype):
+        shape = (int(size),) if shape is None else tuple(int(v) for v in shape)
+        if int(np.prod(shape)) != size:
+            raise ValueError('product of dims must equal N!')
+        self.array_shape, self.axis, self.step = shape, int(axis) % len(shape), float(step)
+        self.view = _axis_view(int(size), shape, self.axis)
+        super().__init__(shape=(size, size), dtype=np.dtype(dtype))
+
+    def _apply(self, x):
+        o, n, i = self.view
+        return K.cumsum(torch.empty_like(x), x, o, n, i, self.step)
+
+    def _adjoint(self, y):
+        o, n, i = self.view
+        return K.cumsum(torch.empty_like(y), y, o, n, i, self.step, adjoint=True)
+
+
+def Integration1D(size: int, shape: Optional[tuple] = None, axis: int = 0, step: float = 1.,
+                  dtype='float64') -> LinearOperator:
+    return Integration1DOperator(size, shape, axis, step, dtype)

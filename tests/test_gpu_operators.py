@@ -320,3 +320,70 @@ def test_entropy_and_barrier_functionals(dtype, tol):
     # Moreau identity through the base class (core/functional.py:207) and the solver-facing scaling 2 * f
     z = np.abs(x[:100]) + 0.5
     assert rel_l2((2 * LogBarrier(100)).fenchel_prox(z, 0.7), (2 * O.LogBarrier(100)).fenchel_prox(z.astype(np.float64), 0.7)) < 10 * tol
+
+
+def test_quadratic_form():
+    """QuadraticForm (reference func/penalty.py:925-990): value x^T Q x and gradient 2 Q x with Q = L^T L built from
+    this package's operators, and as the smooth term of a forward-backward solve."""
+    from pycsou_b200.func.penalty import QuadraticForm
+    from pycsou_b200.linop.diff import Laplacian
+    r = rng(13)
+    shape, n = (24, 30), 720
+    Lp = Laplacian(shape=shape)
+    Lp.lipschitz_cst = Lp.diff_lipschitz_cst = 8.0
+    Q = Lp.H * Lp
+    Q.lipschitz_cst = Q.diff_lipschitz_cst = 64.0
+    x = r.standard_normal(n)
+    Lo = O.Laplacian(shape)
+    Qx = Lo.rmatvec(Lo.matvec(x))
+    F = QuadraticForm(n, linop=Q)
+    assert np.isclose(F(x), np.dot(x, Qx), rtol=1e-12) and rel_l2(F.gradient(x), 2 * Qx) < 1e-13
+    assert F.diff_lipschitz_cst == 128.0
+    F0 = QuadraticForm(n)
+    assert np.isclose(F0(x), np.dot(x, x), rtol=1e-13) and rel_l2(F0.gradient(x), 2 * x) < 1e-15 and F0.diff_lipschitz_cst == 2
+
+
+@pytest.mark.parametrize('shape', [(30, 44), (6, 10, 12)])
+def test_directional_derivatives(shape):
+    """First/SecondDirectionalDerivative, DirectionalGradient, DirectionalLaplacian (reference diff.py:380-774) against
+    the oracle restatement of pylops' Sum * Diagonal(v) * Gradient, constant and per-pixel direction fields."""
+    from pycsou_b200.linop.diff import (DirectionalGradient, DirectionalLaplacian, FirstDirectionalDerivative,
+                                         SecondDirectionalDerivative)
+    r = rng(21)
+    nd, n = len(shape), int(np.prod(shape))
+    x, y = r.standard_normal(n), r.standard_normal(n)
+    v_const = r.standard_normal(nd)
+    v_const /= np.linalg.norm(v_const)
+    v_field = r.standard_normal((nd,) + shape)
+    for v in (v_const, v_field):
+        for kind in ('centered', 'forward'):
+            D, Do = FirstDirectionalDerivative(shape, v, step=0.5, kind=kind), O.FirstDirectionalDerivative(shape, v, step=0.5, kind=kind)
+            assert rel_l2(D(x), Do.matvec(x)) < 1e-13 and rel_l2(D.adjoint(y), Do.rmatvec(y)) < 1e-13
+        D2, D2o = SecondDirectionalDerivative(shape, v), O.SecondDirectionalDerivative(shape, v)
+        assert rel_l2(D2(x), D2o.matvec(x)) < 1e-12 and rel_l2(D2.adjoint(y), D2o.rmatvec(y)) < 1e-12
+        assert abs(np.dot(D2(x), y) - np.dot(x, D2.adjoint(y))) < 1e-9 * n
+    D1, D1b = FirstDirectionalDerivative(shape, v_const), FirstDirectionalDerivative(shape, v_field)
+    DG = DirectionalGradient([D1, D1b])
+    assert DG.shape == (2 * n, n)
+    assert rel_l2(DG(x), np.concatenate([D1(x), D1b(x)])) < 1e-15
+    S1, S2 = SecondDirectionalDerivative(shape, v_const), SecondDirectionalDerivative(shape, v_field)
+    DL = DirectionalLaplacian([S1, S2], weights=[3., 0.5])
+    assert rel_l2(DL(x), S1(x) + 0.5 * S2(x)) < 1e-13           # sic: the first weight is not applied (diff.py:770-773)
+
+
+@pytest.mark.parametrize('dtype,tol', [('float64', 1e-12), ('float32', 2e-5)])
+def test_integration1d(dtype, tol):
+    """Integration1D (reference diff.py:1071-1137): every axis position, short and long contiguous lines, adjointness."""
+    from pycsou_b200.linop.diff import Integration1D
+    r = rng(31)
+    for shape, axis in (((24,), 0), ((5000,), 0), ((40, 30), 0), ((40, 30), 1), ((3, 4100), 1), ((6, 7, 9), 1), ((6, 7, 9), -1)):
+        n = int(np.prod(shape))
+        x, y = r.standard_normal(n).astype(dtype), r.standard_normal(n).astype(dtype)
+        A = Integration1D(n, shape if len(shape) > 1 else None, axis=axis, step=0.25, dtype=dtype)
+        Ao = O.Integration1D(n, shape if len(shape) > 1 else None, axis=axis, step=0.25)
+        assert rel_l2(A(x), Ao.matvec(x.astype(np.float64))) < tol
+        assert rel_l2(A.adjoint(y), Ao.rmatvec(y.astype(np.float64))) < tol
+        lhs, rhs = np.dot(A(x).astype(np.float64), y), np.dot(x, A.adjoint(y).astype(np.float64))
+        assert abs(lhs - rhs) < (1e-9 if dtype == 'float64' else 1e-2) * max(1.0, abs(lhs))
+    sig = np.array([0, 0, 0, 1, 0, 0, 0, 0, 0, 2, 0, 0, 0, 0, -1, 0, 0, 0, 0, 2, 0, 0, 0, 0], dtype=dtype)
+    assert np.array_equal(Integration1D(sig.size, dtype=dtype)(sig), np.cumsum(sig))       # the docstring's example signal
