@@ -11,6 +11,7 @@
 //                optional fused "- y" (residual r = A x - y of the data term).
 #include "pcs_common.cuh"
 #include <type_traits>
+#include <stdlib.h>
 
 using namespace pcs;
 
@@ -135,6 +136,154 @@ __global__ void __launch_bounds__(C2_BX * C2_BY) conv2d_direct_kernel(T* __restr
     }
 }
 
+// Register-tiled form for filters up to KM x KM taps (KM = 7, 15): a thread owns 8 rows x 2 adjacent columns.  For every
+// pair of sample columns it loads a 22-sample run of each (one 64/128-bit shared load per row) and feeds 4 FMAs per
+// sample and filter row: ~0.15 shared loads per FMA instead of 1.1 in the kernel above (which stays for larger filters).
+// The filter sits in shared memory in correlation order, embedded in a KM x (KM + 2) array with a zero column on either
+// side, so the two outputs of a thread read taps b-1, b, b+1 without bounds checks.
+constexpr int C2R_TW = 64, C2R_TH = 64, C2R_RP = 8;
+#ifndef C2R_PACKED_F32
+#define C2R_PACKED_F32 1
+#endif
+__device__ __forceinline__ unsigned long long c2_pack2(float lo, float hi) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void c2_unpack2(unsigned long long v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ unsigned long long c2_fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+#ifndef C2R_MINB_F32
+#define C2R_MINB_F32 3
+#endif
+template <typename T, int KM>
+__global__ void __launch_bounds__(256, sizeof(T) == 4 ? C2R_MINB_F32 : 1) conv2d_reg_kernel(T* __restrict__ out, const T* __restrict__ x,
+                                                         const T* __restrict__ h, int kh, int kw, int off0, int off1,
+                                                         int sgn, const T* __restrict__ sub, int64_t H, int64_t W) {
+    constexpr int KP = KM + 2, SH = C2R_TH + KM - 1, SW = C2R_TW + KM + 1, NS = C2R_RP + KM - 1;
+    typedef typename std::conditional<sizeof(T) == 4, float2, double2>::type V2;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* taps = reinterpret_cast<T*>(smem_raw);                 // [KM][KP], column index b + 1
+    T* tile = taps + ((KM * KP + 3) / 4) * 4;                 // [SH][SW], 16-byte aligned
+    const int tid = threadIdx.x;
+    for (int e = tid; e < KM * KP; e += 256) {
+        const int a = e / KP, b = e - a * KP - 1;
+        T g = T(0);
+        if (a < kh && b >= 0 && b < kw) g = (sgn > 0) ? h[a * kw + b] : h[(kh - 1 - a) * kw + (kw - 1 - b)];
+        taps[e] = g;
+    }
+    const int ca = (sgn > 0) ? off0 : kh - 1 - off0, cb = (sgn > 0) ? off1 : kw - 1 - off1;
+    const int64_t R0 = (int64_t)blockIdx.y * C2R_TH, C0 = (int64_t)blockIdx.x * C2R_TW;
+    {   // tile load: warp <-> rows, lane <-> columns (row pointer and row validity computed once per row)
+        const int lane = tid & 31, wrp = tid >> 5;
+        for (int lr = wrp; lr < SH; lr += 8) {
+            const int64_t r = R0 - ca + lr;
+            const bool rv = r >= 0 && r < H;
+            const T* xr = x + (rv ? r : 0) * W;
+            T* trw = tile + lr * SW;
+#pragma unroll
+            for (int lc = lane; lc < SW; lc += 32) {
+                const int64_t c = C0 - cb + lc;
+                trw[lc] = (rv && c >= 0 && c < W) ? xr[c] : T(0);
+            }
+        }
+    }
+    __syncthreads();
+    const int tx = tid & 31, ty = tid >> 5;
+    T acc0[C2R_RP], acc1[C2R_RP];
+#pragma unroll
+    for (int j = 0; j < C2R_RP; ++j) acc0[j] = acc1[j] = T(0);
+    const T* trow = tile + (ty * C2R_RP) * SW + 2 * tx;
+    if constexpr (sizeof(T) == 4 && C2R_PACKED_F32) {
+        // packed fp32 (fma.rn.f32x2 = SASS FFMA2): one instruction updates the two outputs (col, col+1) of a row:
+        // acc2[j] += (s0, s0) * (g[b], g[b-1]) + (s1, s1) * (g[b+1], g[b]); half the FMA issue slots of the scalar form
+        unsigned long long acc2[C2R_RP];
+#pragma unroll
+        for (int j = 0; j < C2R_RP; ++j) acc2[j] = 0ull;
+#pragma unroll 1
+        for (int beta = 0; beta < KM + 1; beta += 2) {
+            unsigned long long p0[NS], p1[NS];
+#pragma unroll
+            for (int j = 0; j < NS; ++j) {
+                const float2 v = *reinterpret_cast<const float2*>(trow + j * SW + beta);
+                p0[j] = c2_pack2(v.x, v.x);
+                p1[j] = c2_pack2(v.y, v.y);
+            }
+            const T* tp = taps + beta;
+#pragma unroll
+            for (int a = 0; a < KM; ++a) {
+                const float gm = tp[a * KP], g0 = tp[a * KP + 1], gp = tp[a * KP + 2];
+                const unsigned long long t0 = c2_pack2(g0, gm), t1 = c2_pack2(gp, g0);
+#pragma unroll
+                for (int j = 0; j < C2R_RP; ++j) {
+                    acc2[j] = c2_fma2(p0[j + a], t0, acc2[j]);
+                    acc2[j] = c2_fma2(p1[j + a], t1, acc2[j]);
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < C2R_RP; ++j) {
+            float lo, hi;
+            c2_unpack2(acc2[j], lo, hi);
+            acc0[j] = lo; acc1[j] = hi;
+        }
+    } else
+#pragma unroll 1
+    for (int beta = 0; beta < KM + 1; beta += 2) {
+        T s0[NS], s1[NS];
+#pragma unroll
+        for (int j = 0; j < NS; ++j) {
+            const V2 v = *reinterpret_cast<const V2*>(trow + j * SW + beta);
+            s0[j] = v.x; s1[j] = v.y;
+        }
+        const T* tp = taps + beta;                            // tp[a * KP + 0 / 1 / 2] = taps b = beta-1 / beta / beta+1
+#pragma unroll
+        for (int a = 0; a < KM; ++a) {
+            const T gm = tp[a * KP], g0 = tp[a * KP + 1], gp = (beta + 1 < KM) ? tp[a * KP + 2] : T(0);
+#pragma unroll
+            for (int j = 0; j < C2R_RP; ++j) {
+                acc0[j] += g0 * s0[j + a];
+                acc0[j] += gp * s1[j + a];
+                acc1[j] += gm * s0[j + a];
+                acc1[j] += g0 * s1[j + a];
+            }
+        }
+    }
+    const int64_t c = C0 + 2 * tx;
+    const bool pair = (W % 2 == 0) && c + 1 < W;
+#pragma unroll
+    for (int j = 0; j < C2R_RP; ++j) {
+        const int64_t r = R0 + ty * C2R_RP + j;
+        if (r >= H || c >= W) continue;
+        T v0 = acc0[j], v1 = acc1[j];
+        const int64_t idx = r * W + c;
+        if (sub != nullptr) { v0 -= sub[idx]; if (c + 1 < W) v1 -= sub[idx + 1]; }
+        if (pair) {
+            V2 o; o.x = v0; o.y = v1;
+            *reinterpret_cast<V2*>(out + idx) = o;
+        } else {
+            out[idx] = v0;
+            if (c + 1 < W) out[idx + 1] = v1;
+        }
+    }
+}
+template <typename T, int KM>
+static int conv2d_reg_launch(T* out, const T* x, const T* h, int kh, int kw, int off0, int off1, int sgn, const T* sub,
+                             int64_t H, int64_t W, cudaStream_t s, const char* what) {
+    constexpr int KP = KM + 2, SH = C2R_TH + KM - 1, SW = C2R_TW + KM + 1;
+    const size_t smem = ((size_t)((KM * KP + 3) / 4) * 4 + (size_t)SH * SW) * sizeof(T);
+    if (smem > 48 * 1024)
+        cudaFuncSetAttribute(conv2d_reg_kernel<T, KM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    dim3 grid((unsigned)((W + C2R_TW - 1) / C2R_TW), (unsigned)((H + C2R_TH - 1) / C2R_TH));
+    conv2d_reg_kernel<T, KM><<<grid, 256, smem, s>>>(out, x, h, kh, kw, off0, off1, sgn, sub, H, W);
+    return check_launch(what);
+}
+
 template <typename T>
 static int conv2d_direct_launch(T* out, const T* x, const T* h, int kh, int kw, int off0, int off1, int sgn, int64_t H,
                                 int64_t W, cudaStream_t s, const char* what) {
@@ -142,6 +291,11 @@ static int conv2d_direct_launch(T* out, const T* x, const T* h, int kh, int kw, 
     PCS_REQUIRE(off0 >= 0 && off0 < kh && off1 >= 0 && off1 < kw, "%s: offset outside the filter", what);
     if (H * W == 0) return PCS_OK;
     PCS_REQUIRE(out && x && h && out != x, "%s: null or aliased pointer", what);
+    static const bool no_reg = [] { const char* e = getenv("PCS_CONV2D_NO_REGTILE"); return e && atoi(e) != 0; }();
+    if (!no_reg && ((uintptr_t)out % (2 * sizeof(T))) == 0) {
+        if (kh <= 7 && kw <= 7) return conv2d_reg_launch<T, 7>(out, x, h, kh, kw, off0, off1, sgn, nullptr, H, W, s, what);
+        if (kh <= 15 && kw <= 15) return conv2d_reg_launch<T, 15>(out, x, h, kh, kw, off0, off1, sgn, nullptr, H, W, s, what);
+    }
     const size_t smem = ((size_t)kh * kw + (size_t)(C2_TH + kh - 1) * (C2_TW + kw - 1)) * sizeof(T);
     PCS_REQUIRE(smem <= C2_SMEM_LIMIT, "%s: filter %dx%d too large for the direct kernel", what, kh, kw);
     cudaFuncSetAttribute(conv2d_direct_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C2_SMEM_LIMIT);

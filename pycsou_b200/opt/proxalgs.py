@@ -414,6 +414,31 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
             x, z = self._generic_step(x, z, self._scratch_row)
         return {'primal_variable': x, 'dual_variable': z}
 
+    # -- resumability: the state of a solve is (x, z, tau, sigma, rho) ------------------------
+    def save_checkpoint(self, path: str):
+        """Write the current iterates and step sizes to ``path`` (``torch.save``); single-GPU solvers."""
+        if self._slab is not None:
+            raise NotImplementedError('checkpoints of slab-decomposed solves: save each rank\'s iterand')
+        if getattr(self, '_state', None) is None:
+            raise RuntimeError('nothing to checkpoint: call iterate() first')
+        x, z = self._state
+        torch.save({'primal_variable': x.cpu(), 'dual_variable': None if z is None else z.cpu(), 'updates': int(self.iter),
+                    'tau': float(self.tau), 'sigma': None if self.sigma is None else float(self.sigma),
+                    'rho': float(self.rho), 'dim': int(self.dim)}, path)
+
+    def load_checkpoint(self, path: str) -> int:
+        """Warm-start this solver from a checkpoint: the next ``iterate()`` continues from the saved iterates with the
+        saved step sizes.  Returns the number of updates the checkpointed solve had done."""
+        ck = torch.load(path)
+        if ck['dim'] != self.dim:
+            raise ValueError('checkpoint of a problem of another size')
+        self._user_x0, self._user_z0 = ck['primal_variable'], ck['dual_variable']
+        self.tau, self.rho = ck['tau'], ck['rho']
+        if ck['sigma'] is not None:
+            self.sigma = ck['sigma']
+        self.reset()
+        return ck['updates']
+
     def _diag_row(self, it):
         d = self._diag_host[it]
         row = {'Iter': it, 'Relative Improvement (primal variable)': self._rel(float(d[0]), float(d[1]))}

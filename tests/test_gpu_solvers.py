@@ -331,3 +331,28 @@ def test_c4_fused_with_momentum_and_steps():
         out[fused] = est
     assert rel_l2(out[True]['primal_variable'], out[False]['primal_variable']) < 1e-12
     assert rel_l2(out[True]['dual_variable'], out[False]['dual_variable']) < 1e-12
+
+
+def test_checkpoint_resume_is_bit_identical(tmp_path):
+    """save_checkpoint / load_checkpoint: 8 + 12 updates through a checkpoint file == 20 updates in one go."""
+    from pycsou_b200.func.loss import SquaredL2Loss
+    from pycsou_b200.func.penalty import L21Norm, NonNegativeOrthant
+    from pycsou_b200.linop.conv import Convolve2D
+    from pycsou_b200.opt.proxalgs import PDS
+    shape = (60, 140)
+    _, psf, y = synth.tv_deconv_problem(shape, None, 0.02, 3)
+    N = y.size
+
+    def mk(k):
+        F = (1 / 2) * SquaredL2Loss(dim=N, data=y) * Convolve2D(size=N, filter=psf, shape=shape)
+        return PDS(dim=N, F=F, G=NonNegativeOrthant(dim=N), H=0.02 * L21Norm(dim=2 * N, groups=np.tile(np.arange(N), 2)),
+                   K=tv_K(shape), beta=1.0, max_iter=k - 1, min_iter=k - 1, accuracy_threshold=0, verbose=None)
+    full, _, _ = mk(20).iterate()
+    a = mk(8)
+    a.iterate()
+    a.save_checkpoint(str(tmp_path / 'ck.pt'))
+    b = mk(12)
+    assert b.load_checkpoint(str(tmp_path / 'ck.pt')) == 8
+    res, _, _ = b.iterate()
+    assert np.array_equal(res['primal_variable'], full['primal_variable'])
+    assert np.array_equal(res['dual_variable'], full['dual_variable'])
