@@ -66,6 +66,12 @@ PCS_DECL_REAL(pcs_reduce_diffsumsq, (const void* x, const void* y, int64_t n, vo
                                      void* stream))
 PCS_DECL_REAL(pcs_reduce_dot, (const void* x, const void* y, int64_t n, void* out_f64, void* workspace, void* stream))
 PCS_DECL_REAL(pcs_reduce_minmax, (const void* x, int64_t n, void* out2_f64, void* workspace, void* stream))
+/* One Newton step t' = (S(t) - radius) / (C(t) + c0) on g(t) = sum max(|x_i| - t, 0) - radius - c0 t (S, C = sum and
+ * count of the |x_i| above t).  state4_f64 = two (S, C) slots; the step reads slot src_slot (-1: t = 0) and writes
+ * dst_slot.  Replaces the brentq bracket of proj_l1_ball (math/prox.py:160-164; radius > 0, c0 = 0) and the sort +
+ * cumulative sum of SquaredL1Norm.prox (func/penalty.py:310-316; radius = 0, c0 = 1 / (2 tau)). */
+PCS_DECL_REAL(pcs_threshold_newton_step, (const void* x, int64_t n, double radius, double c0, void* state4_f64,
+                                          int src_slot, int dst_slot, void* workspace, void* stream))
 /* LogBarrier / ShannonEntropy / KLDivergence values (func/penalty.py:819-822, 899-903; func/loss.py:659-664): +inf
  * outside the domain */
 PCS_DECL_REAL(pcs_reduce_neglog, (const void* x, int64_t n, void* out_f64, void* workspace, void* stream))

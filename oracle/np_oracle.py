@@ -46,6 +46,17 @@ def proj_l2_ball(x, radius):
     return x if nrm <= radius else radius * x / nrm
 
 
+def proj_l1_ball(x, radius):
+    """math/prox.py:157-164: the argument itself when feasible, else soft-thresholding at the brentq root of
+    mu -> sum max(|x| - mu, 0) - radius on [0, max|x|]."""
+    from scipy import optimize as sciop
+    if np.sum(np.abs(x)) <= radius:
+        return x
+    mu_star = sciop.brentq(lambda mu: np.sum(np.clip(np.abs(x) - mu, a_min=0, a_max=None)) - radius,
+                           a=0, b=np.max(np.abs(x)))
+    return soft(x, mu_star)
+
+
 def proj_linfty_ball(x, radius):
     """math/prox.py:253-256 (the reference clips in place; the oracle works on a copy)."""
     y = np.array(x, copy=True)
@@ -581,6 +592,58 @@ def power_iteration_lipschitz(op, n_iter=200, seed=0):
             return 0.0
         v = w / s
     return float(np.sqrt(s))
+
+
+class LInftyNorm(LpNorm):
+    """func/penalty.py:380-417."""
+    _proj = staticmethod(proj_l1_ball)
+
+    def __call__(self, x):
+        return np.max(np.abs(x))
+
+
+def L1Ball(dim, radius):
+    """func/penalty.py:375-377."""
+    return Indicator(dim, lambda x: np.sum(np.abs(x)) <= radius, lambda x: proj_l1_ball(x, radius=radius))
+
+
+class SquaredL1Norm(Prox):
+    """func/penalty.py:248-317 (both prox computations)."""
+
+    def __init__(self, dim, prox_computation='sort'):
+        self.dim, self.prox_computation = dim, prox_computation
+
+    def __call__(self, x):
+        return np.sum(np.abs(x)) ** 2
+
+    def prox(self, x, tau):
+        if self.prox_computation == 'root':                                  # :300-309
+            from scipy import optimize as sciop
+            if not np.linalg.norm(x) > 0:
+                return x
+            lam = lambda mu: np.clip(np.abs(x) * np.sqrt(tau / mu) - 2 * tau, a_min=0, a_max=None)
+            mu_star = sciop.brentq(lambda mu: np.sum(lam(mu)) - 1, a=1e-12, b=np.max(np.abs(x) ** 2) / (4 * tau))
+            return lam(mu_star) * x / (lam(mu_star) + 2 * tau)
+        y = np.sort(np.abs(x))[::-1]                                         # :310-316
+        csum = np.cumsum(y)
+        factor = 2 * tau / (1 + (np.arange(y.size) + 1) * 2 * tau)
+        k = np.max(np.nonzero(y - factor * csum > 0))
+        return soft(x, factor[k] * csum[k])
+
+
+def RealLine(dim):
+    """func/penalty.py:715-717."""
+    return Indicator(dim, lambda x: bool(np.all(np.isreal(x))), lambda x: np.real(x))
+
+
+def ImagLine(dim):
+    """func/penalty.py:765-767 (the prox is np.imag(x): a REAL array)."""
+    return Indicator(dim, lambda x: bool(np.all(np.real(x) == 0)), lambda x: np.imag(x))
+
+
+def ConsistencyLoss(dim, data):
+    """func/loss.py:584-586."""
+    return Indicator(dim, lambda x: bool(np.allclose(x, data)), lambda x: data)
 
 
 class LogBarrier(Prox):

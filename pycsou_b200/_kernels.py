@@ -209,6 +209,29 @@ def minmax(x):
     return out
 
 
+def threshold_newton(x, radius, c0, batch=4, max_steps=4096):
+    """Exact root ``t`` of ``sum max(|x| - t, 0) = radius + c0 t`` by monotone Newton steps on the device (the l1-ball
+    and squared-l1 thresholds; see ``pcs_threshold_newton_step``).  ``batch`` steps are enqueued between host reads;
+    the iteration has converged when the count of entries above the threshold stops changing."""
+    _chk(x); _real_only(x, 'threshold_newton')
+    state = torch.zeros(4, dtype=torch.float64, device=x.device)
+    name, ws, st = 'pcs_threshold_newton_step' + sfx(x), ptr(reduce_ws(x.device)), stream()
+    src, dst, done = -1, 0, 0
+    while done < max_steps:
+        for _ in range(batch):
+            _lib.call(name, ptr(x), x.numel(), float(radius), float(c0), ptr(state), src, dst, ws, st)
+            src, dst = dst, 1 - dst
+        done += batch
+        vals = state.tolist()
+        (s_new, c_new), (s_old, c_old) = (vals[2 * src], vals[2 * src + 1]), (vals[2 * dst], vals[2 * dst + 1])
+        t_new = max((s_new - radius) / (c_new + c0), 0.0) if c_new + c0 > 0 else 0.0
+        t_old = max((s_old - radius) / (c_old + c0), 0.0) if c_old + c0 > 0 else 0.0
+        # same active set, or an entry within rounding of the root flipping in and out of it
+        if c_new == c_old or abs(t_new - t_old) <= 4e-16 * abs(t_new):
+            return t_new
+    raise RuntimeError('threshold_newton did not converge')
+
+
 def sumgroupnorm(x, n_groups, n_comp):
     _chk(x)
     out = _red_out(x)

@@ -384,6 +384,45 @@ template <typename T> static int pcs_reduce_minmax_impl(const T* x, int64_t n, d
 PCS_EXPORT_REAL(pcs_reduce_minmax, (const void* x, int64_t n, void* out2_f64, void* workspace, void* stream),
                 ((const T*)x, n, (double*)out2_f64, workspace, (cudaStream_t)stream))
 
+// One Newton step on g(t) = sum_i max(|x_i| - t, 0) - radius - t*c0 (convex, piecewise linear, decreasing), started at
+// t = 0: t' = (S(t) - radius) / (C(t) + c0) with S = sum of |x_i| over {|x_i| > t}, C = the size of that set.  The steps
+// increase monotonically and reach the EXACT root after finitely many (the active set can only shrink; it is Michelot's
+// algorithm).  radius > 0, c0 = 0: the threshold of the l1-ball projection, which the reference brackets with brentq
+// (math/prox.py:160-164).  radius = 0, c0 = 1/(2 tau): the threshold of the squared-l1 prox, which the reference finds
+// by a sort and a cumulative sum (func/penalty.py:310-316).  The step reads the previous (S, C) from `state[2*src]`
+// on the device (src < 0: t = 0), so a batch of steps needs no host round trip.
+template <typename T>
+__global__ void __launch_bounds__(RD_BLOCK) threshold_newton_kernel(const T* __restrict__ x, int64_t n, double radius,
+                                                                    double c0, double* state, int src, int dst,
+                                                                    double* partials, unsigned int* ticket) {
+    __shared__ double sm[RD_BLOCK / 32];
+    double t = 0.0;
+    if (src >= 0) t = fmax((__ldcg(&state[2 * src]) - radius) / (__ldcg(&state[2 * src + 1]) + c0), 0.0);
+    const int64_t stride = (int64_t)gridDim.x * RD_BLOCK;
+    double acc[2] = {0.0, 0.0};
+    for (int64_t i = (int64_t)blockIdx.x * RD_BLOCK + threadIdx.x; i < n; i += stride) {
+        const double a = fabs((double)x[i]);
+        if (a > t) { acc[0] += a; acc[1] += 1.0; }
+    }
+    grid_sum_finish<2, RD_BLOCK>(acc, partials, ticket, state + 2 * dst, sm);
+}
+
+template <typename T>
+static int pcs_threshold_newton_step_impl(const T* x, int64_t n, double radius, double c0, double* state, int src,
+                                          int dst, void* ws, cudaStream_t s) {
+    PCS_REQUIRE(n >= 0 && state && ws && (n == 0 || x), "pcs_threshold_newton_step: bad arguments");
+    PCS_REQUIRE(src >= -1 && src <= 1 && dst >= 0 && dst <= 1 && src != dst, "pcs_threshold_newton_step: slots are 0/1");
+    int grid = grid_for(n, RD_BLOCK, RD_CTAS_PER_SM);
+    double* partials = (double*)ws;
+    unsigned int* ticket = (unsigned int*)(partials + 4 * (int64_t)pcs::num_sms() * 8);
+    threshold_newton_kernel<T><<<grid, RD_BLOCK, 0, s>>>(x, n, radius, c0, state, src, dst, partials, ticket);
+    return check_launch("pcs_threshold_newton_step");
+}
+PCS_EXPORT_REAL(pcs_threshold_newton_step,
+                (const void* x, int64_t n, double radius, double c0, void* state4_f64, int src_slot, int dst_slot,
+                 void* workspace, void* stream),
+                ((const T*)x, n, radius, c0, (double*)state4_f64, src_slot, dst_slot, workspace, (cudaStream_t)stream))
+
 // sum over groups of the group 2-norm, planes layout (L21Norm.__call__, func/penalty.py:548-549)
 template <typename T>
 __global__ void __launch_bounds__(RD_BLOCK) sumgroupnorm_kernel(const T* __restrict__ x, int64_t G, int C, int cplx,

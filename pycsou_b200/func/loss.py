@@ -15,7 +15,7 @@ from .. import _kernels as K
 from .._array import to_device
 from ..core.functional import DifferentiableFunctional, ProxFuncPreComp, ProximableFunctional
 from .base import IndicatorFunctional
-from .penalty import L1Norm, L2Ball, L2Norm, LInftyBall, SquaredL2Norm
+from .penalty import (L1Ball, L1Norm, L2Ball, L2Norm, LInftyBall, LInftyNorm, SquaredL1Norm, SquaredL2Norm)
 
 __all__ = ['ProximableLoss', 'DifferentiableLoss', 'L2Loss', 'SquaredL2Loss', 'L2BallLoss', 'L1Loss', 'SquaredL1Loss',
            'L1BallLoss', 'LInftyLoss', 'LInftyBallLoss', 'ConsistencyLoss', 'KLDivergence']
@@ -60,17 +60,36 @@ def LInftyBallLoss(dim: int, data, radius: Number = 1) -> ProximableFunctional:
     return ProximableLoss(LInftyBall(dim=dim, radius=radius), data=data)
 
 
-def _out_of_scope(name):
-    def ctor(*args, **kwargs):
-        raise NotImplementedError(f'{name} is outside the B200 hot path (SURVEY.md section 2 / 8(f) rank 2)')
-    ctor.__name__ = name
-    return ctor
+def SquaredL1Loss(dim: int, data, prox_computation='sort') -> ProximableFunctional:
+    """``||y - x||_1^2`` (reference ``func/loss.py:329-368``)."""
+    return ProximableLoss(SquaredL1Norm(dim=dim, prox_computation=prox_computation), data=data)
 
 
-SquaredL1Loss = _out_of_scope('SquaredL1Loss')
-L1BallLoss = _out_of_scope('L1BallLoss')
-LInftyLoss = _out_of_scope('LInftyLoss')
-ConsistencyLoss = _out_of_scope('ConsistencyLoss')
+def L1BallLoss(dim: int, data, radius: Number = 1) -> ProximableFunctional:
+    """Indicator of ``||y - x||_1 <= radius`` (reference ``func/loss.py:371-426``)."""
+    return ProximableLoss(L1Ball(dim=dim, radius=radius), data=data)
+
+
+def LInftyLoss(dim: int, data) -> ProximableFunctional:
+    """``||y - x||_inf`` (reference ``func/loss.py:429-475``)."""
+    return ProximableLoss(LInftyNorm(dim=dim), data=data)
+
+
+def ConsistencyLoss(dim: int, data) -> IndicatorFunctional:
+    """Indicator of ``x == y`` up to ``np.allclose``'s default tolerances; prox returns the data (reference
+    ``func/loss.py:536-586``)."""
+    def y_like(x):
+        if isinstance(data, Number):
+            return torch.full_like(x, data)
+        return to_device(data).to(device=x.device, dtype=x.dtype).reshape(-1)
+
+    def cond(x):
+        yy = y_like(x)
+        return bool(torch.all(torch.abs(x - yy) <= 1e-8 + 1e-5 * torch.abs(yy)).item())
+
+    def proj(x):
+        return y_like(x).clone()
+    return IndicatorFunctional(dim=dim, condition_func=cond, projection_func=proj, kind='consistency')
 
 
 class KLDivergence(ProximableFunctional):

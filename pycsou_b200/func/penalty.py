@@ -1,7 +1,7 @@
 r"""Penalty functionals on the device (mirror of the hot-path part of ``pycsou/func/penalty.py``).
 
-In scope: ``L2Norm, SquaredL2Norm, L2Ball, L1Norm, LInftyBall, L21Norm, NonNegativeOrthant,
-Segment``.  The remaining reference penalties (sort / root-find / Lambert-W proxes) raise ``NotImplementedError``.
+Every penalty of the reference module is here: the hot-path ones and the leaves of 8(f)
+rank 2 (root-find / Lambert-W proxes run on the device too).
 """
 from __future__ import annotations
 
@@ -13,7 +13,7 @@ import torch
 
 from .. import _kernels as K
 from ..core.functional import DifferentiableFunctional, ProximableFunctional
-from ..math.prox import proj_l2_ball, proj_linfty_ball, proj_nonnegative_orthant, proj_segment, soft
+from ..math.prox import proj_l1_ball, proj_l2_ball, proj_linfty_ball, proj_nonnegative_orthant, proj_segment, soft
 from .base import IndicatorFunctional, LpNorm
 
 __all__ = ['L2Norm', 'SquaredL2Norm', 'L2Ball', 'L1Norm', 'SquaredL1Norm', 'L1Ball', 'LInftyNorm', 'LInftyBall',
@@ -204,18 +204,63 @@ def Segment(dim: int, a: Number = 0, b: Number = 1):
                                params=(a, b))
 
 
-def _out_of_scope(name):
-    def ctor(*args, **kwargs):
-        raise NotImplementedError(f'{name} is outside the B200 hot path (SURVEY.md section 2 / 8(f) rank 2)')
-    ctor.__name__ = name
-    return ctor
+class SquaredL1Norm(ProximableFunctional):
+    r""":math:`\|x\|_1^2` (reference ``func/penalty.py:248-317``).  The prox is ``soft(x, t)`` with ``t`` the root of
+    ``sum max(|x| - t, 0) = t / (2 tau)``: the reference finds it by a descending sort and a cumulative sum
+    (``prox_computation='sort'``, ``:310-316``) or by brentq on an equivalent equation (``'root'``, ``:300-309``); the
+    device path finds the same root exactly by monotone Newton steps, each one a deterministic reduction
+    (``K.threshold_newton``), whichever option is named.  Real arrays only."""
+
+    def __init__(self, dim: int, prox_computation: str = 'sort'):
+        self.prox_computation = prox_computation
+        super(SquaredL1Norm, self).__init__(dim=dim, data=None, is_differentiable=False, is_linear=False)
+
+    def _apply(self, x):
+        return float(K.sumabs(x).item()) ** 2
+
+    def _prox(self, x, tau):
+        if self.prox_computation not in ('sort', 'root'):
+            return None                      # the reference falls through and returns None (func/penalty.py:296-316)
+        t = K.threshold_newton(x, 0.0, 1.0 / (2.0 * tau))
+        return K.prox_l1(torch.empty_like(x), x, t)
 
 
-SquaredL1Norm = _out_of_scope('SquaredL1Norm')
-L1Ball = _out_of_scope('L1Ball')
-LInftyNorm = _out_of_scope('LInftyNorm')
-RealLine = _out_of_scope('RealLine')
-ImagLine = _out_of_scope('ImagLine')
+def L1Ball(dim: int, radius: Number) -> IndicatorFunctional:
+    """Indicator of the l1 ball; prox = ``proj_l1_ball`` (reference ``func/penalty.py:319-377``)."""
+    return IndicatorFunctional(dim=dim, condition_func=lambda x: float(K.sumabs(x).item()) <= radius,
+                               projection_func=lambda x: proj_l1_ball.device(x, radius=radius),
+                               kind='l1ball', params=(radius,))
+
+
+class LInftyNorm(LpNorm):
+    r""":math:`\max_i |x_i|`; prox ``x - tau * proj_l1_ball(x / tau, 1)`` (reference ``func/penalty.py:380-417``)."""
+
+    def __init__(self, dim: int):
+        super(LInftyNorm, self).__init__(dim=dim, proj_lq_ball=proj_l1_ball)
+
+    def _apply(self, x):
+        mn, mx = K.minmax(x).tolist()
+        return max(abs(mn), abs(mx))
+
+
+def RealLine(dim: int) -> IndicatorFunctional:
+    """Indicator of the real line; prox = real part (reference ``func/penalty.py:671-717``)."""
+    def cond(x):
+        return (not x.is_complex()) or float(K.sumabs(x.imag.contiguous()).item()) == 0.0
+    return IndicatorFunctional(dim=dim, condition_func=cond,
+                               projection_func=lambda x: x.real.contiguous() if x.is_complex() else x,
+                               kind='realline')
+
+
+def ImagLine(dim: int) -> IndicatorFunctional:
+    """Indicator of the imaginary line; prox returns the imaginary part as a real array, as the reference does
+    (``func/penalty.py:720-767``: ``np.imag(x)``)."""
+    def cond(x):
+        re = x.real.contiguous() if x.is_complex() else x
+        return float(K.sumabs(re).item()) == 0.0
+    return IndicatorFunctional(dim=dim, condition_func=cond,
+                               projection_func=lambda x: x.imag.contiguous() if x.is_complex() else torch.zeros_like(x),
+                               kind='imagline')
 
 
 class LogBarrier(ProximableFunctional):

@@ -1,7 +1,7 @@
 r"""Element-wise proximal helpers on the device (mirror of ``pycsou/math/prox.py``).
 
-In scope: ``sign``, ``soft``, ``proj_l2_ball``, ``proj_linfty_ball``, ``proj_nonnegative_orthant``, ``proj_segment``
-(reference ``math/prox.py:17-114, 167-343``).  ``proj_l1_ball`` (serial root find) is outside the hot path and raises.
+``sign``, ``soft``, ``proj_l1_ball``, ``proj_l2_ball``, ``proj_linfty_ball``, ``proj_nonnegative_orthant``,
+``proj_segment`` (reference ``math/prox.py:17-343``).
 Unlike the reference the projections never mutate their argument (the reference's in-place behaviour is an aliasing
 hazard); values are identical.
 """
@@ -45,8 +45,17 @@ def soft(x, tau: Number):
     return K.lincomb2(torch.empty_like(x), 1.0, x, -1.0, K.proj_segment(torch.empty_like(x), x, -tau, tau))
 
 
+@_edge
 def proj_l1_ball(x, radius: Number):
-    raise NotImplementedError('proj_l1_ball (serial root find) is outside the B200 hot path (SURVEY.md section 2)')
+    """``x`` (the same object) if ``||x||_1 <= radius`` else ``soft(x, mu)`` with ``sum max(|x| - mu, 0) = radius``
+    (reference ``math/prox.py:157-164``).  The reference brackets ``mu`` with ``scipy.optimize.brentq`` (absolute
+    tolerance 2e-12); here monotone Newton steps on the device reach the exact root (``K.threshold_newton``), so the
+    two agree to brentq's tolerance.  Real arrays only."""
+    if x.is_complex():
+        raise NotImplementedError('proj_l1_ball: real arrays only on the device')
+    if float(K.sumabs(x).item()) <= radius:
+        return x
+    return K.prox_l1(torch.empty_like(x), x, K.threshold_newton(x, radius, 0.0))
 
 
 @_edge

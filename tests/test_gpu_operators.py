@@ -322,6 +322,59 @@ def test_entropy_and_barrier_functionals(dtype, tol):
     assert rel_l2((2 * LogBarrier(100)).fenchel_prox(z, 0.7), (2 * O.LogBarrier(100)).fenchel_prox(z.astype(np.float64), 0.7)) < 10 * tol
 
 
+@pytest.mark.parametrize('dtype,tol', [('float64', 1e-10), ('float32', 2e-6)])
+def test_l1_ball_linfty_and_squared_l1(dtype, tol):
+    """proj_l1_ball, L1Ball, LInftyNorm, SquaredL1Norm ('sort' and 'root'), RealLine, ImagLine, ConsistencyLoss and
+    the *Loss wrappers over them (reference math/prox.py:117-164, func/penalty.py:248-417, 671-767, func/loss.py:
+    329-475, 536-586): the reference's doctest literals, then the oracle on random vectors.  The device finds the
+    thresholds by exact Newton steps where the reference uses brentq (2e-12) or a sort: 1e-10 is the fp64 bar."""
+    from pycsou_b200.func.loss import ConsistencyLoss, L1BallLoss, LInftyLoss, SquaredL1Loss
+    from pycsou_b200.func.penalty import ImagLine, L1Ball, LInftyNorm, RealLine, SquaredL1Norm
+    from pycsou_b200.math.prox import proj_l1_ball
+    x = np.linspace(-1, 1, 5).astype(dtype)
+    assert np.allclose(proj_l1_ball(x, radius=2), [-0.75, -0.25, 0., 0.25, 0.75], atol=10 * tol, rtol=0)
+    x1 = np.arange(10).astype(dtype)
+    assert SquaredL1Norm(10)(x1) == 2025 and LInftyNorm(10)(x1) == 9 and (3 * LInftyNorm(10))(x1) == 27
+    assert np.allclose(SquaredL1Norm(10, 'sort').prox(x1, tau=1), SquaredL1Norm(10, 'root').prox(x1, tau=1))
+    x2 = (x1 / np.linalg.norm(x1, ord=1)).astype(dtype)
+    ball = L1Ball(10, radius=10)
+    xf = (x2 * 0.999).astype(dtype)
+    assert ball(x1) == np.inf and ball(xf) == 0
+    assert np.isclose(np.linalg.norm(ball.prox(x1, tau=1), ord=1), 10.0, rtol=10 * tol)
+    assert np.array_equal(ball.prox(xf, tau=1), xf)
+    r = rng(21)
+    n = 50001
+    xs = (3 * r.standard_normal(n)).astype(dtype)
+    xs[::7] = 0
+    xs[5::11] = xs[3]                                # ties at and around the threshold
+    x64 = xs.astype(np.float64)
+    for radius in (0.3, 40.0, 9000.0, 1e7):
+        assert rel_l2(proj_l1_ball(xs, radius), O.proj_l1_ball(x64, radius)) < tol
+        assert rel_l2(L1Ball(n, radius).prox(xs, 1.0), O.L1Ball(n, radius).prox(x64, 1.0)) < tol
+    for tau in (1e-6, 0.02, 0.9, 30.0):
+        assert rel_l2(LInftyNorm(n).prox(xs, tau), O.LInftyNorm(n).prox(x64, tau)) < tol
+        for how in ('sort', 'root'):
+            assert rel_l2(SquaredL1Norm(n, how).prox(xs, tau), O.SquaredL1Norm(n, 'sort').prox(x64, tau)) < tol
+        assert rel_l2((2 * LInftyNorm(n)).fenchel_prox(xs, tau), (2 * O.LInftyNorm(n)).fenchel_prox(x64, tau)) < 10 * tol
+    assert np.isclose(SquaredL1Norm(n)(xs), O.SquaredL1Norm(n)(x64), rtol=10 * tol)
+    assert LInftyNorm(n)(xs) == O.LInftyNorm(n)(x64)
+    assert np.array_equal(SquaredL1Norm(4).prox(np.zeros(4, dtype=dtype), 1.0), np.zeros(4))
+    y = r.standard_normal(n).astype(dtype)
+    y64 = y.astype(np.float64)
+    shift = lambda f: O.PreCompShift(f, y64)
+    assert rel_l2(L1BallLoss(n, y, radius=25.0).prox(xs, 1.0), shift(O.L1Ball(n, 25.0)).prox(x64, 1.0)) < tol
+    assert rel_l2(LInftyLoss(n, y).prox(xs, 0.4), shift(O.LInftyNorm(n)).prox(x64, 0.4)) < tol
+    assert rel_l2(SquaredL1Loss(n, y).prox(xs, 0.4), shift(O.SquaredL1Norm(n)).prox(x64, 0.4)) < tol
+    cdt = 'complex128' if dtype == 'float64' else 'complex64'
+    xc = (np.arange(10) + 1j).astype(cdt)
+    assert (RealLine(10)(xc), RealLine(10)(np.real(xc).astype(dtype))) == (np.inf, 0)
+    assert np.array_equal(RealLine(10).prox(xc, tau=1), np.real(xc))
+    assert (ImagLine(10)(xc), ImagLine(10)((1j * np.imag(xc)).astype(cdt))) == (np.inf, 0)
+    assert np.array_equal(ImagLine(10).prox(xc, tau=1), np.imag(xc))
+    loss = ConsistencyLoss(10, x1)
+    assert (loss(2 * x1), loss(x1)) == (np.inf, 0) and np.array_equal(loss.prox(2 * x1, tau=1), x1)
+
+
 def test_quadratic_form():
     """QuadraticForm (reference func/penalty.py:925-990): value x^T Q x and gradient 2 Q x with Q = L^T L built from
     this package's operators, and as the smooth term of a forward-backward solve."""

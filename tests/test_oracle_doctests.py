@@ -174,3 +174,27 @@ def test_entropy_and_barrier_functionals():
     k = O.KLDivergence(10, np.arange(10))
     assert k(2 * np.arange(10)) == 13.80837687480246
     assert np.array_equal(np.round(k.prox(2 * np.arange(10), tau=1)), [0, 2, 4, 6, 8, 10, 12, 14, 16, 18])
+
+
+def test_l1_ball_linfty_and_squared_l1():
+    # math/prox.py:143-147 (proj_l1_ball); func/penalty.py:262-269 (SquaredL1Norm), :355-362 (L1Ball), :393-398
+    # (LInftyNorm), :704-709 (RealLine), :755-758 (ImagLine); func/loss.py:571-577 (ConsistencyLoss)
+    x = np.linspace(-1, 1, 5)
+    assert np.allclose(O.proj_l1_ball(x, radius=2), [-0.75, -0.25, 0., 0.25, 0.75], atol=1e-11, rtol=0)
+    assert np.isclose(np.linalg.norm(O.proj_l1_ball(x, radius=2), ord=1), 2.0, atol=1e-11, rtol=0)
+    x1 = np.arange(10)
+    assert O.SquaredL1Norm(10, 'sort')(x1) == 2025
+    assert np.allclose(O.SquaredL1Norm(10, 'sort').prox(x1, tau=1), O.SquaredL1Norm(10, 'root').prox(x1, tau=1))
+    x2 = x1 / np.linalg.norm(x1, ord=1)
+    ball = O.L1Ball(10, radius=10)
+    assert (ball(x1), ball(x2)) == (np.inf, 0)
+    assert np.isclose(np.linalg.norm(ball.prox(x1, tau=1), ord=1), 10.0, atol=1e-10, rtol=0)
+    assert np.allclose(ball.prox(x2, tau=1), x2)
+    assert O.LInftyNorm(10)(x1) == 9
+    xc = np.arange(10) + 1j
+    assert (O.RealLine(10)(xc), O.RealLine(10)(np.real(xc))) == (np.inf, 0)
+    assert np.allclose(O.RealLine(10).prox(xc, tau=1), np.real(xc))
+    assert (O.ImagLine(10)(xc), O.ImagLine(10)(1j * np.imag(xc))) == (np.inf, 0)
+    assert np.allclose(O.ImagLine(10).prox(xc, tau=1), np.imag(xc))
+    loss = O.ConsistencyLoss(10, x1)
+    assert (loss(2 * x1), loss(x1)) == (np.inf, 0) and np.allclose(loss.prox(2 * x1, tau=1), x1)

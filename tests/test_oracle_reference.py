@@ -80,3 +80,24 @@ def test_entropy_and_barrier_match_reference(ref):
     assert P.LogBarrier(50)(xp) == O.LogBarrier(50)(xp) and P.LogBarrier(50)(x) == O.LogBarrier(50)(x) == np.inf
     assert P.ShannonEntropy(50)(xp) == O.ShannonEntropy(50)(xp)
     assert L.KLDivergence(50, d)(xp) == O.KLDivergence(50, d)(xp)
+
+
+def test_l1_ball_linfty_and_squared_l1_match_reference(ref):
+    from pycsou.func import penalty as P, loss as L
+    from pycsou.math import prox as M
+    rng = np.random.default_rng(8)
+    x = 3 * rng.standard_normal(200)
+    for radius in (0.5, 7.0, 1e4):
+        assert np.array_equal(M.proj_l1_ball(x.copy(), radius), O.proj_l1_ball(x, radius))
+        assert np.array_equal(P.L1Ball(200, radius).prox(x.copy(), 1.0), O.L1Ball(200, radius).prox(x, 1.0))
+        assert P.L1Ball(200, radius)(x) == O.L1Ball(200, radius)(x)
+    for tau in (0.01, 0.4, 5.0):
+        assert np.array_equal(P.LInftyNorm(200).prox(x.copy(), tau), O.LInftyNorm(200).prox(x, tau))
+        for how in ('sort', 'root'):
+            assert np.array_equal(P.SquaredL1Norm(200, how).prox(x.copy(), tau), O.SquaredL1Norm(200, how).prox(x, tau))
+    assert P.LInftyNorm(200)(x) == O.LInftyNorm(200)(x) and P.SquaredL1Norm(200)(x) == O.SquaredL1Norm(200)(x)
+    xc = x[:100] + 1j * x[100:]
+    assert np.array_equal(P.RealLine(100).prox(xc, 1.0), O.RealLine(100).prox(xc, 1.0))
+    assert np.array_equal(P.ImagLine(100).prox(xc, 1.0), O.ImagLine(100).prox(xc, 1.0))
+    assert P.RealLine(100)(xc) == O.RealLine(100)(xc) and P.ImagLine(100)(1j * x[:100]) == O.ImagLine(100)(1j * x[:100])
+    assert L.ConsistencyLoss(200, x)(x + 1) == O.ConsistencyLoss(200, x)(x + 1) == np.inf
