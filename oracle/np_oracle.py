@@ -768,3 +768,149 @@ class Integration1D:
     def rmatvec(self, y):
         Y = np.flip(y.reshape(self.dims), axis=self.axis)
         return (self.step * np.flip(np.cumsum(Y, axis=self.axis), axis=self.axis)).reshape(-1)
+
+
+# --------------------------------------------------------------------------------------------------
+# linop/base.py:636-712 (PolynomialLinearOperator); linop/diff.py:222-377, 960-1068 (generalised derivatives)
+# --------------------------------------------------------------------------------------------------
+class PolynomialLinearOperator:
+    """P(L) = sum_k a_k L^k by repeated application (linop/base.py:695-712); the adjoint of a SYMMETRIC-flagged L is
+    the forward map itself (:703-704), else the same recursion on L's adjoint with conjugated coefficients."""
+
+    def __init__(self, L, coeffs, is_symmetric=False):
+        self.L, self.coeffs, self.is_symmetric, self.shape = L, np.asarray(coeffs, dtype=float), is_symmetric, L.shape
+
+    def _horner(self, x, apply):
+        z, y = x.astype(float), self.coeffs[0] * x
+        for c in self.coeffs[1:]:
+            z = apply(z)
+            y = y + c * z
+        return y
+
+    def matvec(self, x):
+        return self._horner(x, self.L.matvec)
+
+    def rmatvec(self, y):
+        return self.matvec(y) if self.is_symmetric else self._horner(y, self.L.rmatvec)
+
+
+class _AffineOfOp:
+    """a * Id + b * L (core/linop.py:442-485 sums and scalings)."""
+
+    def __init__(self, a, b, L):
+        self.a, self.b, self.L, self.shape = a, b, L, L.shape
+
+    def matvec(self, x):
+        return self.a * x + self.b * self.L.matvec(x)
+
+    def rmatvec(self, y):
+        return self.a * y + self.b * self.L.rmatvec(y)
+
+
+class _Power:
+    """L ** N = L * (L * ...) (core/map.py:319-327)."""
+
+    def __init__(self, L, N):
+        self.L, self.N, self.shape = L, int(N), L.shape
+
+    def matvec(self, x):
+        for _ in range(self.N):
+            x = self.L.matvec(x)
+        return x
+
+    def rmatvec(self, y):
+        for _ in range(self.N):
+            y = self.L.rmatvec(y)
+        return y
+
+
+class _KillEdges:
+    """DiagonalOperator(kill_edges) * Dgen (linop/diff.py:374-376, 1065-1067)."""
+
+    def __init__(self, mask, L):
+        self.m, self.L, self.shape = mask.reshape(-1), L, L.shape
+
+    def matvec(self, x):
+        return self.m * self.L.matvec(x)
+
+    def rmatvec(self, y):
+        return self.L.rmatvec(self.m * y)
+
+
+def GeneralisedDerivative(size, shape=None, axis=0, step=1.0, edge=True, dtype='float64', kind_op='iterated',
+                          kind_diff='centered', **kwargs):
+    """linop/diff.py:334-377."""
+    D = FirstDerivative(size, shape, axis, step, edge, dtype, kind_diff)
+    D2 = SecondDerivative(size, shape, axis, step, edge, dtype)
+    if kind_op == 'iterated':
+        Dgen, order = _Power(D, kwargs['order']), kwargs['order']
+    elif kind_op == 'sobolev':
+        Dgen, order = _Power(_AffineOfOp(kwargs['constant'] ** 2, -1.0, D2), kwargs['order']), 2 * kwargs['order']
+    elif kind_op == 'exponential':
+        Dgen, order = _Power(_AffineOfOp(kwargs['constant'], 1.0, D), kwargs['order']), kwargs['order']
+    elif kind_op == 'polynomial':
+        Dgen, order = PolynomialLinearOperator(D, kwargs['coeffs'], is_symmetric=False), len(kwargs['coeffs']) - 1
+    else:
+        raise NotImplementedError
+    kill = np.ones(size if shape is None else shape)
+    kill = np.swapaxes(kill, axis, 0) if axis > 0 else kill
+    if kind_diff in ('forward', 'centered'):
+        kill[-order:] = 0
+    if kind_diff in ('backward', 'centered'):
+        kill[:order] = 0
+    kill = np.swapaxes(kill, 0, axis) if axis > 0 else kill
+    return _KillEdges(np.ascontiguousarray(kill), Dgen)
+
+
+def GeneralisedLaplacian(shape, step=1., edge=True, dtype='float64', kind='iterated', **kwargs):
+    """linop/diff.py:1038-1068 (the Laplacian is FLAGGED symmetric, :1039, whatever its edge rows)."""
+    Delta = Laplacian(shape, step=step, edge=edge, dtype=dtype)
+    if kind == 'iterated':
+        Dgen, order = _Power(Delta, kwargs['order']), 2 * kwargs['order']
+    elif kind == 'sobolev':
+        Dgen, order = _Power(_AffineOfOp(kwargs['constant'] ** 2, -1.0, Delta), kwargs['order']), 2 * kwargs['order']
+    elif kind == 'polynomial':
+        Dgen, order = PolynomialLinearOperator(Delta, kwargs['coeffs'], is_symmetric=True), 2 * (len(kwargs['coeffs']) - 1)
+    else:
+        raise NotImplementedError
+    kill = np.ones(shape)
+    for ax in range(len(shape)):
+        idx = [slice(None)] * len(shape)
+        idx[ax] = slice(0, order)
+        kill[tuple(idx)] = 0
+        idx[ax] = slice(shape[ax] - order, None)
+        kill[tuple(idx)] = 0
+    return _KillEdges(kill, Dgen)
+
+
+class Pooling:
+    """linop/sampling.py:394-536 -> skimage.measure.block_reduce(image, block_size, func, cval=0): the array is padded
+    with zeros up to a multiple of the block size, every block is summed or averaged over its FULL size; the adjoint
+    repeats each pooled value over its block and crops (:529-536; not rescaled for 'mean').  skimage is not in this
+    image, so this restatement is pinned by the reference's doctest literals (:405-424) only."""
+
+    def __init__(self, shape, block_size, pooling_func='mean'):
+        if len(shape) != len(block_size):
+            raise ValueError(f'Inconsistent block size {block_size} for array of shape {shape}.')
+        if pooling_func not in ['mean', 'sum', 'average']:
+            raise ValueError('pooling_func must be one of: "mean" or "sum".')
+        self.input_shape, self.block_size, self.func = tuple(shape), tuple(block_size), pooling_func
+        self.output_shape = tuple(-(-d // b) for d, b in zip(shape, block_size))
+        self.shape = (int(np.prod(self.output_shape)), int(np.prod(shape)))
+
+    def matvec(self, x):
+        pad = [(0, o * b - d) for d, b, o in zip(self.input_shape, self.block_size, self.output_shape)]
+        X = np.pad(np.asarray(x).reshape(self.input_shape), pad, mode='constant', constant_values=0)
+        split = [v for o, b in zip(self.output_shape, self.block_size) for v in (o, b)]
+        blocks = X.reshape(split)
+        axes = tuple(range(1, 2 * len(self.block_size), 2))
+        return (np.mean(blocks, axis=axes) if self.func == 'mean' else np.sum(blocks, axis=axes)).reshape(-1)
+
+    def rmatvec(self, y):
+        X = np.copy(np.asarray(y).reshape(self.output_shape))
+        for ax in range(len(self.input_shape)):
+            X = np.repeat(X, self.block_size[ax], axis=ax)
+            idx = [slice(None)] * X.ndim
+            idx[ax] = slice(0, self.input_shape[ax])
+            X = X[tuple(idx)]
+        return X.reshape(-1)

@@ -198,3 +198,20 @@ def test_l1_ball_linfty_and_squared_l1():
     assert np.allclose(O.ImagLine(10).prox(xc, tau=1), np.imag(xc))
     loss = O.ConsistencyLoss(10, x1)
     assert (loss(2 * x1), loss(x1)) == (np.inf, 0) and np.allclose(loss.prox(2 * x1, tau=1), x1)
+
+
+def test_pooling_doctest():
+    # linop/sampling.py:405-424
+    x = np.arange(24).reshape(4, 6)
+    P = O.Pooling(x.shape, (2, 3), 'mean')
+    assert P.output_shape == (2, 2) and np.array_equal(P.matvec(x.flatten()).reshape(2, 2), [[4., 7.], [16., 19.]])
+    assert np.array_equal(P.rmatvec(P.matvec(x.flatten())).reshape(4, 6),
+                          np.repeat(np.repeat([[4., 7.], [16., 19.]], 2, axis=0), 3, axis=1))
+    P = O.Pooling(x.shape, (2, 3), 'sum')
+    assert np.array_equal(P.matvec(x.flatten()).reshape(2, 2), [[24, 42], [96, 114]])
+    assert np.array_equal(P.rmatvec(P.matvec(x.flatten())).reshape(4, 6),
+                          np.repeat(np.repeat([[24, 42], [96, 114]], 2, axis=0), 3, axis=1))
+    P = O.Pooling((5, 7), (2, 3), 'mean')          # ragged: zero padding counts in the mean
+    X = np.arange(35.).reshape(5, 7)
+    assert P.output_shape == (3, 3) and P.matvec(X.flatten())[-1] == X[4, 6] / 6
+    assert P.rmatvec(np.arange(9.)).shape == (35,)

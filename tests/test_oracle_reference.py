@@ -101,3 +101,28 @@ def test_l1_ball_linfty_and_squared_l1_match_reference(ref):
     assert np.array_equal(P.ImagLine(100).prox(xc, 1.0), O.ImagLine(100).prox(xc, 1.0))
     assert P.RealLine(100)(xc) == O.RealLine(100)(xc) and P.ImagLine(100)(1j * x[:100]) == O.ImagLine(100)(1j * x[:100])
     assert L.ConsistencyLoss(200, x)(x + 1) == O.ConsistencyLoss(200, x)(x + 1) == np.inf
+
+
+def test_generalised_derivatives_match_reference(ref):
+    """GeneralisedDerivative / GeneralisedLaplacian / PolynomialLinearOperator run live on the pylops stand-in."""
+    from pycsou.linop.diff import GeneralisedDerivative as GD, GeneralisedLaplacian as GL
+    rng = np.random.default_rng(9)
+    x, y = rng.standard_normal(60), rng.standard_normal(60)
+    cases = [dict(kind_op='iterated', order=3), dict(kind_op='sobolev', order=2, constant=0.3),
+             dict(kind_op='exponential', order=3, constant=-0.2),
+             dict(kind_op='polynomial', coeffs=0.5 * np.array([1e-2, 0, -0.2, 0, 1]))]
+    for kw in cases:
+        for kind_diff in ('forward', 'backward', 'centered'):
+            A, Ao = GD(size=60, kind_diff=kind_diff, **kw), O.GeneralisedDerivative(60, kind_diff=kind_diff, **kw)
+            assert np.allclose(A(x), Ao.matvec(x), rtol=1e-13, atol=1e-13)
+            assert np.allclose(A.adjoint(y), Ao.rmatvec(y), rtol=1e-13, atol=1e-13)
+        A = GD(size=60, shape=(6, 10), axis=1, step=0.5, **kw)
+        Ao = O.GeneralisedDerivative(60, shape=(6, 10), axis=1, step=0.5, **kw)
+        assert np.allclose(A(x), Ao.matvec(x), rtol=1e-13, atol=1e-13)
+        assert np.allclose(A.adjoint(y), Ao.rmatvec(y), rtol=1e-13, atol=1e-13)
+    x, y = rng.standard_normal(20 * 22), rng.standard_normal(20 * 22)
+    for kw in (dict(kind='iterated', order=2), dict(kind='sobolev', order=2, constant=0.4),
+               dict(kind='polynomial', coeffs=[0.5, -1.0, 0.25])):
+        A, Ao = GL(shape=(20, 22), **kw), O.GeneralisedLaplacian((20, 22), **kw)
+        assert np.allclose(A(x), Ao.matvec(x), rtol=1e-13, atol=1e-13)
+        assert np.allclose(A.adjoint(y), Ao.rmatvec(y), rtol=1e-13, atol=1e-13)
