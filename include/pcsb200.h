@@ -136,6 +136,12 @@ int pcs_take(void* out, const void* x, const void* idx_i64, int64_t outer, int64
              int elem_bytes, void* stream);
 int pcs_put(void* out, const void* y, const void* idx_i64, int64_t outer, int64_t n, int64_t m, int64_t inner,
             int elem_bytes, void* stream);
+/* Pooling / unpooling (linop/sampling.py:525-536 -> skimage block_reduce with zero padding; np.repeat + crop): C-order
+ * array of d0 x d1 x d2 samples (1 for unused leading axes), blocks b0 x b1 x b2; scale = 1 (sum) or 1/(b0 b1 b2). */
+PCS_DECL_REAL(pcs_pool_fwd, (void* out, const void* x, int64_t d0, int64_t d1, int64_t d2, int64_t b0, int64_t b1,
+                             int64_t b2, double scale, void* stream))
+PCS_DECL_REAL(pcs_pool_adj, (void* out, const void* y, int64_t d0, int64_t d1, int64_t d2, int64_t b0, int64_t b1,
+                             int64_t b2, void* stream))
 int64_t pcs_mask_workspace_bytes(int64_t n);
 int pcs_mask_count(const void* mask_u8, int64_t n, void* workspace, void* total_out_i64, void* stream);
 int pcs_mask_indices(const void* mask_u8, int64_t n, const void* workspace, void* idx_out_i64, void* stream);

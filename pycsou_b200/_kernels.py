@@ -361,6 +361,19 @@ def put(out, y, idx, outer, n, inner):
     return out
 
 
+def pool_fwd(out, x, dims, block, scale):
+    """Block sum / mean of a C-order array of up to three axes (``dims``, ``block`` padded to length 3 with ones)."""
+    _chk(out, x); _real_only(x, 'Pooling')
+    _lib.call('pcs_pool_fwd' + sfx(x), ptr(out), ptr(x), *map(int, dims), *map(int, block), float(scale), stream())
+    return out
+
+
+def pool_adj(out, y, dims, block):
+    _chk(out, y); _real_only(y, 'Pooling')
+    _lib.call('pcs_pool_adj' + sfx(y), ptr(out), ptr(y), *map(int, dims), *map(int, block), stream())
+    return out
+
+
 def mask_to_indices(mask_u8: torch.Tensor) -> torch.Tensor:
     """Sorted positions of the set entries of a uint8 device mask (construction-time; one host sync)."""
     _chk(mask_u8)

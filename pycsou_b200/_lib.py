@@ -38,6 +38,8 @@ REAL = {
     'pcs_reduce_diffsumsq': [P, P, I64, P, P, P],
     'pcs_reduce_dot': [P, P, I64, P, P, P],
     'pcs_reduce_minmax': [P, I64, P, P, P],
+    'pcs_pool_fwd': [P, P, I64, I64, I64, I64, I64, I64, F64, P],
+    'pcs_pool_adj': [P, P, I64, I64, I64, I64, I64, I64, P],
     'pcs_threshold_newton_step': [P, I64, F64, F64, P, I32, I32, P, P],
     'pcs_reduce_sumgroupnorm': [P, I64, I32, I32, P, P, P],
     'pcs_scale_by_norm': [P, P, P, F64, I32, I64, P],

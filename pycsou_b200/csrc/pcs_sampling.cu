@@ -169,3 +169,74 @@ extern "C" int pcs_mask_indices(const void* mask_u8, int64_t n, const void* work
         (const uint8_t*)mask_u8, n, (const int64_t*)workspace, (int64_t*)idx_out_i64);
     return check_launch("pcs_mask_indices");
 }
+
+// ------------------------------------------------------------------------------------------------ block pooling
+// Pooling (reference linop/sampling.py:394-536 -> skimage.measure.block_reduce with cval = 0): the array (up to three
+// axes, C order) is tiled by blocks of b0 x b1 x b2 samples, ragged border blocks being completed with zeros; every
+// block is summed (scale = 1) or averaged over the FULL block size (scale = 1 / (b0 b1 b2)).  One thread per pooled
+// sample, fp64 accumulation; the threads of a warp walk neighbouring blocks of one row, so their reads cover one
+// contiguous span of 32 * b2 samples per block row.
+struct PoolGeo { int64_t d[3], b[3], o[3]; };
+
+template <typename T>
+__global__ void __launch_bounds__(SG_BLOCK) pool_fwd_kernel(T* __restrict__ out, const T* __restrict__ x, PoolGeo g,
+                                                            double scale) {
+    const int64_t total = g.o[0] * g.o[1] * g.o[2];
+    for (int64_t t = (int64_t)blockIdx.x * SG_BLOCK + threadIdx.x; t < total; t += (int64_t)gridDim.x * SG_BLOCK) {
+        const int64_t k = t % g.o[2], j = (t / g.o[2]) % g.o[1], i = t / (g.o[2] * g.o[1]);
+        const int64_t i1 = min((i + 1) * g.b[0], g.d[0]), j1 = min((j + 1) * g.b[1], g.d[1]),
+                      k1 = min((k + 1) * g.b[2], g.d[2]);
+        double acc = 0.0;
+        for (int64_t a = i * g.b[0]; a < i1; ++a)
+            for (int64_t b = j * g.b[1]; b < j1; ++b) {
+                const T* row = x + (a * g.d[1] + b) * g.d[2];
+                for (int64_t c = k * g.b[2]; c < k1; ++c) acc += (double)row[c];
+            }
+        out[t] = (T)(acc * scale);
+    }
+}
+
+// "Unpooling" (linop/sampling.py:529-536): every sample of a block receives the block's pooled value (np.repeat along
+// each axis, cropped to the input shape) -- for 'mean' this is NOT rescaled, exactly as the reference does.
+template <typename T>
+__global__ void __launch_bounds__(SG_BLOCK) pool_adj_kernel(T* __restrict__ out, const T* __restrict__ y, PoolGeo g) {
+    const int64_t total = g.d[0] * g.d[1] * g.d[2];
+    for (int64_t t = (int64_t)blockIdx.x * SG_BLOCK + threadIdx.x; t < total; t += (int64_t)gridDim.x * SG_BLOCK) {
+        const int64_t c = t % g.d[2], b = (t / g.d[2]) % g.d[1], a = t / (g.d[2] * g.d[1]);
+        out[t] = y[((a / g.b[0]) * g.o[1] + b / g.b[1]) * g.o[2] + c / g.b[2]];
+    }
+}
+
+static bool pool_geo(PoolGeo& g, int64_t d0, int64_t d1, int64_t d2, int64_t b0, int64_t b1, int64_t b2) {
+    const int64_t d[3] = {d0, d1, d2}, b[3] = {b0, b1, b2};
+    for (int a = 0; a < 3; ++a) {
+        if (d[a] < 1 || b[a] < 1) return false;
+        g.d[a] = d[a]; g.b[a] = b[a]; g.o[a] = (d[a] + b[a] - 1) / b[a];
+    }
+    return true;
+}
+
+template <typename T>
+static int pcs_pool_fwd_impl(T* out, const T* x, int64_t d0, int64_t d1, int64_t d2, int64_t b0, int64_t b1,
+                             int64_t b2, double scale, cudaStream_t s) {
+    PoolGeo g;
+    PCS_REQUIRE(pool_geo(g, d0, d1, d2, b0, b1, b2) && out && x, "pcs_pool_fwd: bad arguments");
+    pool_fwd_kernel<T><<<grid_for(g.o[0] * g.o[1] * g.o[2], SG_BLOCK, 8), SG_BLOCK, 0, s>>>(out, x, g, scale);
+    return check_launch("pcs_pool_fwd");
+}
+template <typename T>
+static int pcs_pool_adj_impl(T* out, const T* y, int64_t d0, int64_t d1, int64_t d2, int64_t b0, int64_t b1,
+                             int64_t b2, cudaStream_t s) {
+    PoolGeo g;
+    PCS_REQUIRE(pool_geo(g, d0, d1, d2, b0, b1, b2) && out && y, "pcs_pool_adj: bad arguments");
+    pool_adj_kernel<T><<<grid_for(d0 * d1 * d2, SG_BLOCK, 8), SG_BLOCK, 0, s>>>(out, y, g);
+    return check_launch("pcs_pool_adj");
+}
+PCS_EXPORT_REAL(pcs_pool_fwd,
+                (void* out, const void* x, int64_t d0, int64_t d1, int64_t d2, int64_t b0, int64_t b1, int64_t b2,
+                 double scale, void* stream),
+                ((T*)out, (const T*)x, d0, d1, d2, b0, b1, b2, scale, (cudaStream_t)stream))
+PCS_EXPORT_REAL(pcs_pool_adj,
+                (void* out, const void* y, int64_t d0, int64_t d1, int64_t d2, int64_t b0, int64_t b1, int64_t b2,
+                 void* stream),
+                ((T*)out, (const T*)y, d0, d1, d2, b0, b1, b2, (cudaStream_t)stream))

@@ -3,7 +3,8 @@ r"""Operator glue (mirror of the hot-path part of ``pycsou/linop/base.py``).
 In scope: ``DiagonalOperator, IdentityOperator, NullOperator, HomothetyMap,
 LinOpStack / LinOpVStack / LinOpHStack`` plus a minimal ``DenseLinearOperator`` (plain library GEMV through
 ``torch.mv`` -- explicit-matrix algebra is not part of the stencil path, it exists so that the reference's LASSO
-example runs).  Sparse / dask / Kronecker / Khatri-Rao / Block / Polynomial operators are out of scope and raise.
+example runs) and ``PolynomialLinearOperator``.  Sparse / dask / Kronecker / Khatri-Rao / Block operators are out of
+scope and raise.
 """
 from __future__ import annotations
 
@@ -202,6 +203,37 @@ class HomothetyMap(DiagonalOperator):
         return self.cst
 
 
+class PolynomialLinearOperator(LinearOperator):
+    r""":math:`P(L)=\sum_k a_k L^k` by repeated application of a square operator (reference ``linop/base.py:636-712``):
+    one application of ``L`` and one fused ``y += a_k z`` pass per degree.  As in the reference, the adjoint of an
+    operator FLAGGED symmetric is the forward map itself (``:703-704``)."""
+
+    def __init__(self, LinOp: LinearOperator, coeffs):
+        self.coeffs = np.asarray(coeffs).astype(LinOp.dtype if LinOp.dtype is not None else 'float64')
+        if np.iscomplexobj(self.coeffs):
+            raise NotImplementedError('complex polynomial coefficients')
+        if LinOp.shape[0] != LinOp.shape[1]:
+            raise ValueError('Input linear operator must be square.')
+        self.Linop = LinOp
+        super(PolynomialLinearOperator, self).__init__(shape=LinOp.shape, dtype=LinOp.dtype,
+                                                       is_explicit=LinOp.is_explicit, is_dense=LinOp.is_dense,
+                                                       is_sparse=LinOp.is_sparse, is_dask=LinOp.is_dask,
+                                                       is_symmetric=LinOp.is_symmetric)
+
+    def _horner(self, x, step):
+        z, y = x, K.scale(torch.empty_like(x), float(self.coeffs[0]), x)
+        for c in self.coeffs[1:]:
+            z = step(z)
+            K.lincomb2(y, 1.0, y, float(c), z)
+        return y
+
+    def _apply(self, x):
+        return self._horner(x, self.Linop._apply)
+
+    def _adjoint(self, y):
+        return self._horner(y, self.Linop._apply if self.is_symmetric else self.Linop._adjoint)
+
+
 def _out_of_scope(name):
     def ctor(*args, **kwargs):
         raise NotImplementedError(f'{name} is outside the B200 hot path (explicit-matrix algebra, SURVEY.md section 2)')
@@ -214,7 +246,6 @@ SparseLinearOperator = _out_of_scope('SparseLinearOperator')
 DaskLinearOperator = _out_of_scope('DaskLinearOperator')
 BlockOperator = _out_of_scope('BlockOperator')
 BlockDiagonalOperator = _out_of_scope('BlockDiagonalOperator')
-PolynomialLinearOperator = _out_of_scope('PolynomialLinearOperator')
 KroneckerProduct = _out_of_scope('KroneckerProduct')
 KroneckerSum = _out_of_scope('KroneckerSum')
 KhatriRaoProduct = _out_of_scope('KhatriRaoProduct')

@@ -4,8 +4,8 @@ r"""Finite-difference operators (mirror of the hot-path part of ``pycsou/linop/d
 (``diff.py:133-219``), ``Gradient`` (default ``kind='centered'``, ``edge=True``; ``diff.py:777-882``) and ``Laplacian``
 (``diff.py:885-957``) keep the reference's signatures and defaults.  Where the reference wraps a pylops operator,
 these factories return device-resident ``LinearOperator`` subclasses whose ``_apply`` / ``_adjoint`` launch the
-stencil kernels of ``csrc/pcs_diff.cu``.  Directional / generalised derivatives and ``Integration1D`` are out of
-scope and raise ``NotImplementedError``.
+stencil kernels of ``csrc/pcs_diff.cu``.  Directional and generalised derivatives and ``Integration1D`` (SURVEY.md
+section 8(f) rank 3) are built on the same kernels.
 """
 from __future__ import annotations
 
@@ -162,14 +162,48 @@ def Laplacian(shape: tuple, weights: Tuple[float] = (1, 1), step: Union[tuple, f
     return LaplacianOperator(shape, weights, step, edge, dtype)
 
 
-def _out_of_scope(name):
-    def ctor(*args, **kwargs):
-        raise NotImplementedError(f'{name} is outside the B200 hot path (SURVEY.md section 2 / 8(f) rank 3)')
-    ctor.__name__ = name
-    return ctor
+def _kill_edges(shape, order, axes, low=True, high=True):
+    """Diagonal mask that zeroes the first / last ``order`` samples along ``axes`` (``diff.py:355-376, 1059-1067``)."""
+    from .base import DiagonalOperator
+    kill = np.ones(shape)
+    for ax in axes:
+        idx = [slice(None)] * kill.ndim
+        if high:                                   # numpy's [-order:] (order 0 selects everything, as in the reference)
+            idx[ax] = slice(-order, None)
+            kill[tuple(idx)] = 0
+        if low:
+            idx[ax] = slice(None, order)
+            kill[tuple(idx)] = 0
+    return DiagonalOperator(kill.reshape(-1))
 
 
-GeneralisedDerivative = _out_of_scope('GeneralisedDerivative')
+def GeneralisedDerivative(size: int, shape: Optional[tuple] = None, axis: int = 0, step: float = 1.0, edge: bool = True,
+                          dtype: str = 'float64', kind_op='iterated', kind_diff='centered', **kwargs) -> LinearOperator:
+    r"""Generalised derivative ``KillEdges * P(D)`` (reference ``diff.py:222-377``): ``kind_op`` = ``'iterated'``
+    (:math:`D^N`), ``'sobolev'`` (:math:`(\alpha^2 I - D^2)^N`), ``'exponential'`` (:math:`(\alpha I + D)^N`) or
+    ``'polynomial'`` (``coeffs``), composed from the stencil kernels op by op."""
+    from .base import IdentityOperator, PolynomialLinearOperator
+    D = FirstDerivative(size=size, shape=shape, axis=axis, step=step, edge=edge, dtype=dtype, kind=kind_diff)
+    D.is_symmetric = False
+    D2 = SecondDerivative(size=size, shape=shape, axis=axis, step=step, edge=edge, dtype=dtype)
+    if kind_op == 'iterated':
+        N = kwargs['order']
+        Dgen, order = D ** N, N
+    elif kind_op == 'sobolev':
+        alpha, N = kwargs['constant'], kwargs['order']
+        Dgen, order = ((alpha ** 2) * IdentityOperator(size=size) - D2) ** N, 2 * N
+    elif kind_op == 'exponential':
+        alpha, N = kwargs['constant'], kwargs['order']
+        Dgen, order = (alpha * IdentityOperator(size=size) + D) ** N, N
+    elif kind_op == 'polynomial':
+        coeffs = kwargs['coeffs']
+        Dgen, order = PolynomialLinearOperator(LinOp=D, coeffs=coeffs), len(coeffs) - 1
+    else:
+        raise NotImplementedError(
+            'Supported generalised derivative types are: iterated, sobolev, exponential, polynomial.')
+    kill = _kill_edges((Dgen.shape[0],) if shape is None else tuple(shape), order, (axis,),
+                       low=kind_diff in ('backward', 'centered'), high=kind_diff in ('forward', 'centered'))
+    return kill * Dgen
 
 
 class FirstDirectionalDerivativeOperator(LinearOperator):
@@ -280,7 +314,26 @@ def DirectionalLaplacian(second_directional_derivatives, weights=None) -> Linear
     for i in range(1, len(second_directional_derivatives)):
         lap += weights[i] * second_directional_derivatives[i]
     return lap
-GeneralisedLaplacian = _out_of_scope('GeneralisedLaplacian')
+def GeneralisedLaplacian(shape: Optional[tuple] = None, step: Union[tuple, float] = 1., edge: bool = True,
+                         dtype: str = 'float64', kind='iterated', **kwargs) -> LinearOperator:
+    r"""Generalised Laplacian ``KillEdges * P(\Delta)`` (reference ``diff.py:960-1068``): ``kind`` = ``'iterated'``,
+    ``'sobolev'`` (:math:`(\alpha^2 I - \Delta)^N`) or ``'polynomial'``.  The Laplacian is flagged symmetric as in the
+    reference (``:1039``), which only matters for the adjoint of the polynomial form."""
+    from .base import IdentityOperator, PolynomialLinearOperator
+    Delta = Laplacian(shape=shape, step=step, edge=edge, dtype=dtype)
+    Delta.is_symmetric = True
+    if kind == 'iterated':
+        N = kwargs['order']
+        Dgen, order = Delta ** N, 2 * N
+    elif kind == 'sobolev':
+        alpha, N = kwargs['constant'], kwargs['order']
+        Dgen, order = ((alpha ** 2) * IdentityOperator(size=shape[0] * shape[1]) - Delta) ** N, 2 * N
+    elif kind == 'polynomial':
+        coeffs = kwargs['coeffs']
+        Dgen, order = PolynomialLinearOperator(LinOp=Delta, coeffs=coeffs), 2 * (len(coeffs) - 1)
+    else:
+        raise NotImplementedError('Supported generalised derivative types are: iterated, sobolev, polynomial.')
+    return _kill_edges(tuple(shape), order, range(len(shape))) * Dgen
 
 
 class Integration1DOperator(LinearOperator):

@@ -5,7 +5,8 @@ r"""Sampling operators (mirror of the hot-path part of ``pycsou/linop/sampling.p
 (``sampling_bool``, ``input_size``, ``nb_of_samples``, ``downsampling_mask``, ``output_shape`` ...).  Masks are
 converted once into a sorted int64 index list on the device (``pcs_mask_count`` / ``pcs_mask_indices``); forward is a
 gather, adjoint a zero-fill + scatter (``csrc/pcs_sampling.cu``).  Masks and indices are bit-exact by construction.
-``Pooling``, ``NNSampling``, ``GeneralisedVandermonde`` and ``MappedDistanceMatrix`` are out of scope and raise.
+``Pooling`` (``sampling.py:394-536``) is a block-reduce kernel.  ``NNSampling``, ``GeneralisedVandermonde`` and
+``MappedDistanceMatrix`` are out of scope and raise.
 """
 from __future__ import annotations
 
@@ -162,6 +163,47 @@ class DownSampling(Masking):
         return mask.reshape(-1)
 
 
+class Pooling(LinearOperator):
+    r"""Sum / mean pooling over constant-size blocks tiling an array of up to three axes (reference
+    ``sampling.py:394-536``, which calls ``skimage.measure.block_reduce`` with zero padding: ragged border blocks are
+    completed with zeros and a mean divides by the FULL block size).  The adjoint is the reference's *unpooling*: the
+    pooled value is repeated over its block and cropped to the input shape, without rescaling (``:529-536``)."""
+
+    def __init__(self, shape: tuple, block_size: Union[tuple, list], pooling_func: str = 'mean',
+                 dtype: type = np.float64):
+        if len(shape) != len(block_size):
+            raise ValueError(f'Inconsistent block size {block_size} for array of shape {shape}.')
+        if pooling_func not in ['mean', 'sum', 'average']:
+            raise ValueError(f'pooling_func must be one of: "mean" or "sum".')
+        if pooling_func == 'average':
+            # the reference stores pooling_func = None for 'average' and block_reduce then fails (sampling.py:503-505)
+            raise NotImplementedError("pooling_func='average' does not work in the reference either; use 'mean'")
+        if len(shape) > 3:
+            raise NotImplementedError('Pooling is implemented for arrays of up to three axes')
+        self.input_shape = tuple(int(d) for d in shape)
+        self.block_size = tuple(int(b) for b in block_size)
+        self.pooling_func = pooling_func
+        self.output_shape = self.get_output_shape()
+        self.output_size = int(np.prod(self.output_shape))
+        self.input_size = int(np.prod(self.input_shape))
+        pad = 3 - len(self.input_shape)
+        self._dims = (1,) * pad + self.input_shape
+        self._block = (1,) * pad + self.block_size
+        self._scale = 1.0 / float(np.prod(self.block_size)) if pooling_func == 'mean' else 1.0
+        super(Pooling, self).__init__(shape=(self.output_size, self.input_size), dtype=dtype)
+
+    def get_output_shape(self) -> tuple:
+        return tuple(-(-d // b) for d, b in zip(self.input_shape, self.block_size))
+
+    def _apply(self, x):
+        out = torch.empty(self.output_size, dtype=x.dtype, device=x.device)
+        return K.pool_fwd(out, x, self._dims, self._block, self._scale)
+
+    def _adjoint(self, y):
+        out = torch.empty(self.input_size, dtype=y.dtype, device=y.device)
+        return K.pool_adj(out, y, self._dims, self._block)
+
+
 def _out_of_scope(name):
     def ctor(*args, **kwargs):
         raise NotImplementedError(f'{name} is outside the B200 hot path (SURVEY.md section 2)')
@@ -169,7 +211,6 @@ def _out_of_scope(name):
     return ctor
 
 
-Pooling = _out_of_scope('Pooling')
 NNSampling = _out_of_scope('NNSampling')
 GeneralisedVandermonde = _out_of_scope('GeneralisedVandermonde')
 MappedDistanceMatrix = _out_of_scope('MappedDistanceMatrix')
