@@ -222,6 +222,8 @@ class SquaredL1Norm(ProximableFunctional):
         if self.prox_computation not in ('sort', 'root'):
             return None                      # the reference falls through and returns None (func/penalty.py:296-316)
         t = K.threshold_newton(x, 0.0, 1.0 / (2.0 * tau))
+        if t <= 0.0:                         # x = 0 ('root' returns x, :308-309; 'sort' raises on the empty argmax)
+            return x.clone()
         return K.prox_l1(torch.empty_like(x), x, t)
 
 
