@@ -260,9 +260,50 @@ def c4_csmri():
     save('c4_csmri_cps', dict(shape=shape, lam=lam, eps=float(eps), tau=1 / 3, sigma=1 / 3, rho=1, m=int(m)), arrays)
 
 
+from tests.oracle_cases import GD_CASES, GL_CASES, LEAF_RADII, LEAF_TAUS, leaf_inputs  # noqa: E402
+
+
+def leaves():
+    """Outputs of the reference's own proxes / operators for the SURVEY 8(f) rank-2 and rank-3 leaves."""
+    from pycsou.func import loss as L, penalty as P
+    from pycsou.linop.diff import GeneralisedDerivative, GeneralisedLaplacian
+    from pycsou.math.prox import proj_l1_ball
+    x, d, y = leaf_inputs()
+    n = x.size
+    arrays = {}
+    for i, tau in enumerate(LEAF_TAUS):
+        arrays[f'logbarrier_{i}'] = P.LogBarrier(n).prox(x.copy(), tau)
+        arrays[f'shannon_{i}'] = P.ShannonEntropy(n).prox(x.copy(), tau)
+        arrays[f'kl_{i}'] = L.KLDivergence(n, d).prox(x.copy(), tau)
+        arrays[f'linfty_{i}'] = P.LInftyNorm(n).prox(x.copy(), tau)
+        arrays[f'sql1_sort_{i}'] = P.SquaredL1Norm(n, 'sort').prox(x.copy(), tau)
+        arrays[f'sql1_root_{i}'] = P.SquaredL1Norm(n, 'root').prox(x.copy(), tau)
+        arrays[f'linfty_loss_{i}'] = L.LInftyLoss(n, y).prox(x.copy(), tau)
+    for i, r in enumerate(LEAF_RADII):
+        arrays[f'l1ball_{i}'] = np.array(proj_l1_ball(x.copy(), r))
+        arrays[f'l1ball_loss_{i}'] = np.array(L.L1BallLoss(n, y, radius=r).prox(x.copy(), 1.0))
+    xp = np.abs(x) + 0.1
+    values = dict(logbarrier=float(P.LogBarrier(n)(xp)), shannon=float(P.ShannonEntropy(n)(xp)),
+                  kl=float(L.KLDivergence(n, d)(xp)), linfty=float(P.LInftyNorm(n)(x)),
+                  sql1=float(P.SquaredL1Norm(n)(x)))
+    for i, kw in enumerate(GD_CASES):
+        for kd in ('forward', 'backward', 'centered'):
+            A = GeneralisedDerivative(size=n, shape=(20, 20), axis=1, step=0.5, kind_diff=kd, **kw)
+            arrays[f'gd_{i}_{kd}_fwd'], arrays[f'gd_{i}_{kd}_adj'] = A(x), A.adjoint(y)
+    for i, kw in enumerate(GL_CASES):
+        A = GeneralisedLaplacian(shape=(20, 20), **kw)
+        arrays[f'gl_{i}_fwd'], arrays[f'gl_{i}_adj'] = A(x), A.adjoint(y)
+    save('leaves_rank23', dict(n=n, seed=31, x_checksum=checksum(x), d_checksum=checksum(d), y_checksum=checksum(y),
+                               values=values), arrays)
+
+
 if __name__ == '__main__':
+    if sys.argv[1:] == ['leaves']:
+        leaves()
+        sys.exit(0)
     c1_lasso()
     c2_tv_denoise()
     c3_tv_deconv()
     misc_solvers()
     c4_csmri()
+    leaves()

@@ -444,6 +444,43 @@ def test_pooling(dtype, tol):
         Pooling((4, 6), (2, 3), 'max')
 
 
+def test_leaves_against_reference_fixture():
+    """The device leaves of SURVEY 8(f) against tests/golden/leaves_rank23.npz (outputs of the reference's own classes,
+    tests/golden/gen_golden.py): fp64, 1e-10 relative L2 measured against ||x|| for the threshold proxes."""
+    from tests import oracle_cases as C
+    from tests.helpers import load_golden
+    from pycsou_b200.func.loss import KLDivergence, L1BallLoss, LInftyLoss
+    from pycsou_b200.func.penalty import LInftyNorm, LogBarrier, ShannonEntropy, SquaredL1Norm
+    from pycsou_b200.linop.diff import GeneralisedDerivative, GeneralisedLaplacian
+    from pycsou_b200.math.prox import proj_l1_ball
+    meta, g = load_golden('leaves_rank23')
+    x, d, y = C.leaf_inputs(meta['n'], meta['seed'])
+    n = x.size
+    err = lambda a, b: float(np.linalg.norm(np.asarray(a) - b) / np.linalg.norm(x))
+    for i, tau in enumerate(C.LEAF_TAUS):
+        assert err(LogBarrier(n).prox(x, tau), g[f'logbarrier_{i}']) < 1e-12
+        assert err(ShannonEntropy(n).prox(x, tau), g[f'shannon_{i}']) < 1e-12
+        assert err(KLDivergence(n, d).prox(x, tau), g[f'kl_{i}']) < 1e-12
+        assert err(LInftyNorm(n).prox(x, tau), g[f'linfty_{i}']) < 1e-10
+        assert err(SquaredL1Norm(n, 'sort').prox(x, tau), g[f'sql1_sort_{i}']) < 1e-10
+        assert err(SquaredL1Norm(n, 'root').prox(x, tau), g[f'sql1_root_{i}']) < 1e-10
+        assert err(LInftyLoss(n, y).prox(x, tau), g[f'linfty_loss_{i}']) < 1e-10
+    for i, r in enumerate(C.LEAF_RADII):
+        assert err(proj_l1_ball(x, r), g[f'l1ball_{i}']) < 1e-10
+        assert err(L1BallLoss(n, y, radius=r).prox(x, 1.0), g[f'l1ball_loss_{i}']) < 1e-10
+    xp, v = np.abs(x) + 0.1, meta['values']
+    assert np.isclose(LogBarrier(n)(xp), v['logbarrier'], rtol=1e-12) and np.isclose(ShannonEntropy(n)(xp), v['shannon'], rtol=1e-12)
+    assert np.isclose(KLDivergence(n, d)(xp), v['kl'], rtol=1e-12) and LInftyNorm(n)(x) == v['linfty']
+    assert np.isclose(SquaredL1Norm(n)(x), v['sql1'], rtol=1e-12)
+    for i, kw in enumerate(C.GD_CASES):
+        for kd in ('forward', 'backward', 'centered'):
+            A = GeneralisedDerivative(size=n, shape=(20, 20), axis=1, step=0.5, kind_diff=kd, **kw)
+            assert rel_l2(A(x), g[f'gd_{i}_{kd}_fwd']) < 1e-12 and rel_l2(A.adjoint(y), g[f'gd_{i}_{kd}_adj']) < 1e-12
+    for i, kw in enumerate(C.GL_CASES):
+        A = GeneralisedLaplacian(shape=(20, 20), **kw)
+        assert rel_l2(A(x), g[f'gl_{i}_fwd']) < 1e-12 and rel_l2(A.adjoint(y), g[f'gl_{i}_adj']) < 1e-12
+
+
 def test_quadratic_form():
     """QuadraticForm (reference func/penalty.py:925-990): value x^T Q x and gradient 2 Q x with Q = L^T L built from
     this package's operators, and as the smooth term of a forward-backward solve."""
