@@ -37,8 +37,8 @@ LAMBDA = 0.02
 NOISE = 0.02
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the fused kernel from the committed `ncu --set full`
 # captures (profiles/r01_ncu_pds_{f32,f64}_v5.txt); bench.py cannot run under ncu itself
-NCU_DRAM_BYTES = {('f32', 4096, 'sep'): 441536768, ('f64', 4096, 'sep'): 962170368}
-NCU_SOURCE = 'profiles/r01_ncu_pds_f32_v9_ws.txt, r01_ncu_pds_f64_v13.txt (ncu --set full, one launch)'
+NCU_DRAM_BYTES = {('f32', 4096, 'sep'): 441034240, ('f64', 4096, 'sep'): 962170368}
+NCU_SOURCE = 'profiles/r01_ncu_pds_f32_v14_ws.txt, r01_ncu_pds_f64_v13.txt (ncu --set full, one launch)'
 
 
 def parse_args():
