@@ -49,6 +49,10 @@ PCS_DECL_REAL(pcs_prox_kl, (void* out, const void* x, const void* data, double t
 /* L21Norm.prox (func/penalty.py:551-557) for groups = tile(arange(n_groups), n_comp); is_complex: interleaved re/im */
 PCS_DECL_REAL(pcs_prox_l21, (void* out, const void* x, double tau, int64_t n_groups, int n_comp, int is_complex,
                              void* stream))
+/* L21Norm.prox (func/penalty.py:551-557) for an ARBITRARY label array (penalty.py:532-546): groups in CSR form --
+ * members_i64[offsets_i64[g] .. offsets_i64[g+1]) are the coordinates of group g (ragged groups of any size) */
+PCS_DECL_REAL(pcs_prox_l21_csr, (void* out, const void* x, double tau, const void* members_i64, const void* offsets_i64,
+                                 int64_t n_groups, int is_complex, void* stream))
 /* out = x * f(sumsq): mode 0 L2Norm.prox (func/penalty.py:23-70), mode 1 proj_l2_ball (math/prox.py:207-210),
  * mode 2 rescale to norm `param` (power iteration, core/linop.py:279-321).  sumsq_f64 = device double holding ||x||^2 */
 PCS_DECL_REAL(pcs_scale_by_norm, (void* out, const void* x, const void* sumsq_f64, double param, int mode, int64_t n,
@@ -80,6 +84,11 @@ PCS_DECL_REAL(pcs_reduce_kl, (const void* x, const void* data, int64_t n, void* 
 /* L21Norm.__call__ (func/penalty.py:548-549) */
 PCS_DECL_REAL(pcs_reduce_sumgroupnorm, (const void* x, int64_t n_groups, int n_comp, int is_complex, void* out_f64,
                                         void* workspace, void* stream))
+
+/* L21Norm.__call__ for an arbitrary label array (CSR groups, see pcs_prox_l21_csr) */
+PCS_DECL_REAL(pcs_reduce_sumgroupnorm_csr, (const void* x, const void* members_i64, const void* offsets_i64,
+                                            int64_t n_groups, int is_complex, void* out_f64, void* workspace,
+                                            void* stream))
 
 /* ---- finite differences: pylops FirstDerivative/SecondDerivative/Gradient/Laplacian behind
  *      pycsou/linop/diff.py:128-130, 218-219, 882, 957.  kind: 0 forward, 1 centered, 2 backward ------------------ */

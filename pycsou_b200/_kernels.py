@@ -240,6 +240,22 @@ def sumgroupnorm(x, n_groups, n_comp):
     return out
 
 
+def prox_l21_csr(out, x, tau, members, offsets):
+    """L21Norm.prox for arbitrary (ragged) groups given in CSR form (int64 device tensors)."""
+    _chk(out, x, members, offsets)
+    _lib.call('pcs_prox_l21_csr' + sfx(x), ptr(real_view(out)), ptr(real_view(x)), float(tau), ptr(members), ptr(offsets),
+              int(offsets.numel()) - 1, int(x.is_complex()), stream())
+    return out
+
+
+def sumgroupnorm_csr(x, members, offsets):
+    _chk(x, members, offsets)
+    out = _red_out(x)
+    _lib.call('pcs_reduce_sumgroupnorm_csr' + sfx(x), ptr(real_view(x)), ptr(members), ptr(offsets),
+              int(offsets.numel()) - 1, int(x.is_complex()), ptr(out), ptr(reduce_ws(x.device)), stream())
+    return out
+
+
 def scale_by_norm(out, x, sumsq_dev, param, mode):
     """mode 0: L2Norm.prox factor max(1 - param/||x||, 0); mode 1: l2-ball projection factor."""
     _chk(out, x)

@@ -33,6 +33,8 @@ REAL = {
     'pcs_reduce_kl': [P, P, I64, P, P, P],
     'pcs_proj_segment': [P, P, F64, F64, I64, P],
     'pcs_prox_l21': [P, P, F64, I64, I32, I32, P],
+    'pcs_prox_l21_csr': [P, P, F64, P, P, I64, I32, P],
+    'pcs_reduce_sumgroupnorm_csr': [P, P, P, I64, I32, P, P, P],
     'pcs_reduce_sumsq': [P, I64, P, P, P],
     'pcs_reduce_sumabs': [P, I64, P, P, P],
     'pcs_reduce_diffsumsq': [P, P, I64, P, P, P],

@@ -457,6 +457,92 @@ PCS_EXPORT_REAL(pcs_reduce_sumgroupnorm,
                  void* stream),
                 ((const T*)x, n_groups, n_comp, is_complex, (double*)out_f64, workspace, (cudaStream_t)stream))
 
+// ---- L21Norm for ARBITRARY label arrays (func/penalty.py:532-560): groups in CSR form ----------------------------------
+// `members` lists the coordinates of group 0, then of group 1, ... (stable order); group g owns members[offsets[g] ..
+// offsets[g+1]).  Groups may be ragged and of any size.  One warp per group: lanes stride over the members, the sum of
+// squares is accumulated in double and warp-reduced (deterministic), then
+//   * prox: out[i] = clip(1 - tau / ||x_g||, 0) * x[i] for every member i            (penalty.py:551-557)
+//   * value: sum_g ||x_g||_2                                                         (penalty.py:548-549)
+template <typename T>
+__device__ __forceinline__ double l21_csr_group_sumsq(const T* __restrict__ x, const int64_t* __restrict__ members,
+                                                      int64_t a, int64_t b, int e, int lane) {
+    double ss = 0.0;
+    for (int64_t k = a + lane; k < b; k += 32) {
+        const int64_t i = members[k] * e;
+        for (int c = 0; c < e; ++c) {
+            const double v = (double)x[i + c];
+            ss = fma(v, v, ss);
+        }
+    }
+    return warp_sum(ss);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(EW_BLOCK) prox_l21_csr_kernel(T* __restrict__ out, const T* __restrict__ x, T tau,
+                                                                const int64_t* __restrict__ members,
+                                                                const int64_t* __restrict__ offsets, int64_t G, int cplx) {
+    const int lane = threadIdx.x & 31, e = cplx ? 2 : 1;
+    const int64_t nwarps = (int64_t)gridDim.x * (EW_BLOCK / 32);
+    for (int64_t g = (int64_t)blockIdx.x * (EW_BLOCK / 32) + (threadIdx.x >> 5); g < G; g += nwarps) {
+        const int64_t a = offsets[g], b = offsets[g + 1];
+        const double ss = l21_csr_group_sumsq<T>(x, members, a, b, e, lane);
+        const T f = l21_factor<T>((T)sqrt(ss), tau);
+        for (int64_t k = a + lane; k < b; k += 32) {
+            const int64_t i = members[k] * e;
+            for (int c = 0; c < e; ++c) out[i + c] = f * x[i + c];
+        }
+    }
+}
+
+template <typename T>
+static int pcs_prox_l21_csr_impl(T* out, const T* x, T tau, const int64_t* members, const int64_t* offsets, int64_t G,
+                                 int cplx, cudaStream_t s) {
+    PCS_REQUIRE(G >= 0, "pcs_prox_l21_csr: negative group count");
+    if (G == 0) return PCS_OK;
+    PCS_REQUIRE(out && x && members && offsets, "pcs_prox_l21_csr: null pointer");
+    prox_l21_csr_kernel<T><<<grid_for(G * 32, EW_BLOCK, EW_CTAS_PER_SM), EW_BLOCK, 0, s>>>(out, x, tau, members, offsets,
+                                                                                          G, cplx);
+    return check_launch("pcs_prox_l21_csr");
+}
+PCS_EXPORT_REAL(pcs_prox_l21_csr,
+                (void* out, const void* x, double tau, const void* members_i64, const void* offsets_i64,
+                 int64_t n_groups, int is_complex, void* stream),
+                ((T*)out, (const T*)x, (T)tau, (const int64_t*)members_i64, (const int64_t*)offsets_i64, n_groups,
+                 is_complex, (cudaStream_t)stream))
+
+template <typename T>
+__global__ void __launch_bounds__(RD_BLOCK) sumgroupnorm_csr_kernel(const T* __restrict__ x,
+                                                                    const int64_t* __restrict__ members,
+                                                                    const int64_t* __restrict__ offsets, int64_t G,
+                                                                    int cplx, double* out, double* partials,
+                                                                    unsigned int* ticket) {
+    __shared__ double sm[RD_BLOCK / 32];
+    const int lane = threadIdx.x & 31, e = cplx ? 2 : 1;
+    const int64_t nwarps = (int64_t)gridDim.x * (RD_BLOCK / 32);
+    double acc[1] = {0.0};
+    for (int64_t g = (int64_t)blockIdx.x * (RD_BLOCK / 32) + (threadIdx.x >> 5); g < G; g += nwarps) {
+        const double ss = l21_csr_group_sumsq<T>(x, members, offsets[g], offsets[g + 1], e, lane);
+        if (lane == 0) acc[0] += sqrt(ss);
+    }
+    grid_sum_finish<1, RD_BLOCK>(acc, partials, ticket, out, sm);
+}
+
+template <typename T>
+static int pcs_reduce_sumgroupnorm_csr_impl(const T* x, const int64_t* members, const int64_t* offsets, int64_t G,
+                                            int cplx, double* out, void* ws, cudaStream_t s) {
+    PCS_REQUIRE(G >= 0 && out && ws && (G == 0 || (x && members && offsets)), "pcs_reduce_sumgroupnorm_csr: bad arguments");
+    double* partials = (double*)ws;
+    unsigned int* ticket = (unsigned int*)(partials + 4 * (int64_t)pcs::num_sms() * 8);
+    sumgroupnorm_csr_kernel<T><<<grid_for(G * 32, RD_BLOCK, RD_CTAS_PER_SM), RD_BLOCK, 0, s>>>(x, members, offsets, G, cplx,
+                                                                                              out, partials, ticket);
+    return check_launch("pcs_reduce_sumgroupnorm_csr");
+}
+PCS_EXPORT_REAL(pcs_reduce_sumgroupnorm_csr,
+                (const void* x, const void* members_i64, const void* offsets_i64, int64_t n_groups, int is_complex,
+                 void* out_f64, void* workspace, void* stream),
+                ((const T*)x, (const int64_t*)members_i64, (const int64_t*)offsets_i64, n_groups, is_complex,
+                 (double*)out_f64, workspace, (cudaStream_t)stream))
+
 // out = x * f(s) where s is a device-resident double: mode 0: f = clip(1 - tau/sqrt(s), 0) (L2Norm.prox,
 // func/penalty.py:23-70 via proj_l2_ball math/prox.py:207-210 -> x - tau*proj(x/tau) = x*max(1 - tau/||x||, 0));
 // mode 1: f = (sqrt(s) <= radius ? 1 : radius/sqrt(s)) (proj_l2_ball); mode 2: f = p/sqrt(s).  s holds ||x||^2.

@@ -88,9 +88,10 @@ class L21Norm(ProximableFunctional):
     ``groups`` is a label array of length ``dim``.  As in the reference, ``__new__`` degenerates to ``L1Norm`` when
     all labels are distinct (or ``groups`` is None) and to ``L2Norm`` when there is a single group
     (``penalty.py:525-530``).  The device kernels implement the *planes* layout ``groups == tile(arange(G), C)``
-    (component ``c`` of group ``g`` at ``x[c*G + g]``) -- the layout of a stacked ``Gradient`` output, i.e. isotropic
-    TV.  Arbitrary label arrays are re-ordered into that layout through a gather/scatter permutation when all groups
-    have the same size; ragged groups raise ``NotImplementedError``.
+    (component ``c`` of group ``g`` at ``x[c*G + g]``, up to 4 components) -- the layout of a stacked ``Gradient``
+    output, i.e. isotropic TV -- with one thread per group.  Any other label array (ragged groups, groups of any size,
+    labels in any order) runs on the segmented kernels ``pcs_prox_l21_csr`` / ``pcs_reduce_sumgroupnorm_csr``: the labels
+    are sorted once at construction into CSR form (members, offsets) and one warp works on each group.
     """
 
     def __new__(cls, dim: int, groups=None):
@@ -112,50 +113,47 @@ class L21Norm(ProximableFunctional):
 
     def __init__(self, dim: int, groups):
         self.groups = groups
-        if isinstance(groups, PlanesGroups):      # O(1) description of tile(arange(G), C): no label array is built
+        self._csr = None                          # (members, offsets) on the device, general label arrays only
+        if isinstance(groups, PlanesGroups) and groups.n_comp <= 4:
+            # O(1) description of tile(arange(G), C): no label array is built
             if groups.size != dim:
                 raise ValueError('groups must have one label per coordinate.')
-            if groups.n_comp > 4:
-                raise NotImplementedError('L21Norm supports at most 4 components per group')
             self.n_groups, self.n_comp = groups.n_groups, groups.n_comp
             self.groups_idxs = groups
-            self._is_planes, self._perm = True, None
+            self._is_planes = True
             super(L21Norm, self).__init__(dim=dim, data=None, is_differentiable=False, is_linear=False)
             return
         g = _labels(groups)
         if g.size != dim:
             raise ValueError('groups must have one label per coordinate.')
         self.groups_idxs, inv, counts = np.unique(g, return_inverse=True, return_counts=True)
+        inv = inv.reshape(-1)
         self.n_groups = int(self.groups_idxs.size)
-        if np.any(counts != counts[0]):
-            raise NotImplementedError('L21Norm with ragged groups is not supported by the device kernels')
-        self.n_comp = int(counts[0])
-        if self.n_comp > 4:
-            raise NotImplementedError('L21Norm supports at most 4 components per group')
-        planes = np.tile(np.arange(self.n_groups), self.n_comp)
-        self._is_planes = bool(np.array_equal(inv, planes))
+        uniform = bool(np.all(counts == counts[0]))
+        self.n_comp = int(counts[0]) if uniform else None
+        # fast path: the planes layout of a stacked Gradient output (isotropic TV), up to 4 components per group
+        self._is_planes = bool(uniform and self.n_comp <= 4 and
+                               np.array_equal(inv, np.tile(np.arange(self.n_groups), self.n_comp)))
         if not self._is_planes:
-            # stable order of members inside each group -> position in the planes layout
-            order = np.argsort(inv, kind='stable').reshape(self.n_groups, self.n_comp)
-            self._perm_host = order.T.reshape(-1).astype(np.int64)      # planes[k] = x[perm[k]]
-        self._perm = None
+            # any other label array (ragged groups, any group size): CSR form, members of a group in index order
+            self._members_host = np.argsort(inv, kind='stable').astype(np.int64)
+            self._offsets_host = np.concatenate(([0], np.cumsum(counts))).astype(np.int64)
         super(L21Norm, self).__init__(dim=dim, data=None, is_differentiable=False, is_linear=False)
 
-    def _to_planes(self, x):
-        if self._is_planes:
-            return x
-        if self._perm is None or self._perm.device != x.device:
-            self._perm = torch.from_numpy(self._perm_host).to(x.device)
-        return K.take(torch.empty_like(x), x, self._perm, 1, x.numel(), 1)
+    def _groups_csr(self, dev):
+        if self._csr is None or self._csr[0].device != dev:
+            self._csr = (torch.from_numpy(self._members_host).to(dev), torch.from_numpy(self._offsets_host).to(dev))
+        return self._csr
 
     def _apply(self, x):
-        return float(K.sumgroupnorm(self._to_planes(x), self.n_groups, self.n_comp).item())
+        if self._is_planes:
+            return float(K.sumgroupnorm(x, self.n_groups, self.n_comp).item())
+        return float(K.sumgroupnorm_csr(x, *self._groups_csr(x.device)).item())
 
     def _prox(self, x, tau):
-        p = K.prox_l21(torch.empty_like(x), self._to_planes(x), tau, self.n_groups, self.n_comp)
         if self._is_planes:
-            return p
-        return K.put(torch.empty_like(x), p, self._perm, 1, x.numel(), 1)
+            return K.prox_l21(torch.empty_like(x), x, tau, self.n_groups, self.n_comp)
+        return K.prox_l21_csr(torch.empty_like(x), x, tau, *self._groups_csr(x.device))
 
 
 class PlanesGroups:

@@ -182,6 +182,55 @@ def test_prox_and_projections(dtype, tol):
     assert abs(P.SquaredL2Norm(n)(x) - np.sum(x64 ** 2)) < 1e3 * tol * n
 
 
+def test_l21norm_reference_doctest_pin():
+    """The reference's own doctest for L21Norm (/root/reference/pycsou/func/penalty.py:494-509): two groups of five."""
+    x = np.arange(10, dtype=np.float64)
+    groups = np.concatenate((np.ones(5), 2 * np.ones(5)))
+    f = P.L21Norm(dim=x.size, groups=groups)
+    assert type(f) is P.L21Norm
+    assert type(P.L21Norm(dim=x.size, groups=np.arange(10))) is P.L1Norm          # penalty.py:497-500
+    assert type(P.L21Norm(dim=x.size, groups=np.ones(10))) is P.L2Norm            # penalty.py:501-504
+    assert abs(f(x) - 21.44594499772297) < 1e-13                                  # penalty.py:505-506
+    tau = 0.5
+    # penalty.py:507-509: prox == per-group L2Norm prox
+    l2 = P.L2Norm(dim=5)
+    expect = np.concatenate((l2.prox(x[0:5], tau=tau), l2.prox(x[5:10], tau=tau)))
+    assert np.allclose(f.prox(x, tau=tau), expect, rtol=1e-14, atol=0)
+    assert rel_l2(f.prox(x, tau), O.L21Norm(10, groups).prox(x, tau)) < 1e-15
+
+
+@pytest.mark.parametrize('dtype,tol', DT)
+def test_l21norm_general_groups(dtype, tol):
+    """Arbitrary label arrays (penalty.py:532-560): ragged groups, groups longer than a warp, labels in any order,
+    a zero group (1 - tau/0 -> -inf -> 0), complex input."""
+    r = rng(11)
+    n = 5000
+    labels = r.integers(0, 37, size=n).astype(np.float64) * 1.5 - 3        # ragged, unordered, non-integer labels
+    labels[:40] = 99.0                                                     # one group that is entirely zero
+    x = r.standard_normal(n).astype(dtype)
+    x[:40] = 0
+    f, fo = P.L21Norm(n, labels), O.L21Norm(n, labels)
+    assert type(f) is P.L21Norm and not f._is_planes
+    x64 = x.astype(np.float64)
+    for tau in (0.3, 5.0, 40.0):
+        assert rel_l2(f.prox(x, tau), fo.prox(x64, tau)) < tol
+    assert abs(f(x) - fo(x64)) < 10 * tol * fo(x64)
+    assert rel_l2((0.2 * f).fenchel_prox(x, 0.7), (0.2 * fo).fenchel_prox(x64, 0.7)) < 10 * tol
+    # many small ragged groups (sizes 1..7) and five-component planes (more than the planes kernel takes)
+    sizes = r.integers(1, 8, size=900)
+    lab2 = r.permutation(np.repeat(np.arange(sizes.size), sizes))
+    x2 = r.standard_normal(lab2.size).astype(dtype)
+    assert rel_l2(P.L21Norm(lab2.size, lab2).prox(x2, 0.8), O.L21Norm(lab2.size, lab2).prox(x2.astype(np.float64), 0.8)) < tol
+    lab3 = np.tile(np.arange(300), 5)
+    x3 = r.standard_normal(lab3.size).astype(dtype)
+    assert rel_l2(P.L21Norm(lab3.size, lab3).prox(x3, 1.1), O.L21Norm(lab3.size, lab3).prox(x3.astype(np.float64), 1.1)) < tol
+    # complex input: |x|^2 over real and imaginary parts (np.linalg.norm of a complex group)
+    ctype = np.complex64 if dtype == 'float32' else np.complex128
+    xc = (r.standard_normal(n) + 1j * r.standard_normal(n)).astype(ctype)
+    assert rel_l2(f.prox(xc, 2.0), fo.prox(xc.astype(np.complex128), 2.0)) < tol
+    assert abs(f(xc) - fo(xc.astype(np.complex128))) < 10 * tol * fo(xc.astype(np.complex128))
+
+
 @pytest.mark.parametrize('dtype,tol', DT)
 def test_loss_gradient_and_composition(dtype, tol):
     from pycsou_b200.func.loss import SquaredL2Loss

@@ -68,8 +68,11 @@ def test_arithmetic_dispatch_and_lipschitz_rules():
     l21 = L21Norm(10, np.tile(np.arange(5), 2))
     assert isinstance(l21, L21Norm) and (l21.n_groups, l21.n_comp, l21._is_planes) == (5, 2, True)
     assert not L21Norm(10, np.repeat(np.arange(5), 2))._is_planes
-    with pytest.raises(NotImplementedError):
-        L21Norm(10, [0, 0, 0, 1, 1, 1, 1, 2, 2, 2])       # ragged
+    rag = L21Norm(10, [0, 0, 0, 1, 1, 1, 1, 2, 2, 2])       # ragged groups: CSR form (members sorted by group, offsets)
+    assert not rag._is_planes and rag.n_groups == 3 and rag.n_comp is None
+    assert rag._offsets_host.tolist() == [0, 3, 7, 10] and rag._members_host.tolist() == list(range(10))
+    perm = L21Norm(6, [5., 2., 5., 2., 9., 9.])             # labels in any order: groups sorted by label value
+    assert perm._members_host.tolist() == [1, 3, 0, 2, 4, 5] and perm._offsets_host.tolist() == [0, 2, 4, 6]
     V = LinOpVStack(G, IdentityOperator(20))
     assert V.shape == (60, 20) and np.isclose(V.lipschitz_cst, np.sqrt(5.))
     assert DiagonalOperator(np.array([-3., 2.])).lipschitz_cst == 2.0      # sic: max, not max|.| (base.py:567)
