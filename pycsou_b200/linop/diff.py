@@ -51,6 +51,10 @@ class FirstDerivativeOperator(LinearOperator):
         self.axis = axis
         super().__init__(shape=(size, size), dtype=np.dtype(dtype))
 
+    def _lipschitz_upper_bound(self):
+        # two entries of magnitude 1/h per row and per column (forward / backward): ||D|| <= 2/h
+        return 2.0 / abs(self.step) if self.kind in ('forward', 'backward') else None
+
     def _apply(self, x):
         return K.firstderiv(torch.empty_like(x), x, self.outer, self.n, self.inner, self.kind, self.edge, self.step)
 
@@ -88,6 +92,12 @@ class GradientOperator(LinearOperator):
         self.edge, self.kind = bool(edge), kind
         self.N = int(np.prod(self.array_shape))
         super().__init__(shape=(nd * self.N, self.N), dtype=np.dtype(dtype))
+
+    def _lipschitz_upper_bound(self):
+        # ||K||^2 <= sum over axes of ||D_axis||^2 <= sum 4 / h_axis^2 (forward / backward differences); sqrt(8) in 2-D
+        if self.kind not in ('forward', 'backward'):
+            return None
+        return float(np.sqrt(sum(4.0 / (h * h) for h in self.steps)))
 
     def _apply(self, x):
         nd, N = len(self.array_shape), self.N

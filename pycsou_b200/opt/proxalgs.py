@@ -44,6 +44,12 @@ def _is_dev_tensor(a):
     return isinstance(a, torch.Tensor) and a.is_cuda
 
 
+def _own_copy(a, dtype):
+    """Device copy of ``a`` that the solver may overwrite (``to_device`` passes device tensors through)."""
+    t = to_device(a, dtype)
+    return t.clone() if isinstance(a, torch.Tensor) and t.data_ptr() == a.data_ptr() else t
+
+
 def _to_host(t: torch.Tensor) -> np.ndarray:
     """Device tensor -> numpy array through a pinned buffer (a pageable read-back runs at a quarter of the PCIe rate).
     The pinned block comes from torch's caching host allocator and goes back to it when the array is dropped."""
@@ -58,14 +64,21 @@ class _DeviceLoop:
 
     _n_metrics = 4          # [||d x||^2, ||x_old||^2, ||d z||^2, ||z_old||^2]
 
-    def _alloc_diag(self):
-        rows = int(max(self.max_iter, self.min_iter)) + 2
+    def _alloc_diag(self, keep=0):
+        """Diagnostics rows of this run; the first ``keep`` rows (updates of an earlier ``iterate()`` that this one
+        continues, core/solver.py:64-66) are preserved."""
+        rows = max(int(max(self.max_iter, self.min_iter)) + 2, int(keep) + 1)
         dev = getattr(self, '_diag_dev', None)
         if dev is not None and dev.shape[0] == rows and dev.device == device():
-            dev.zero_()                      # buffers (one of them pinned) are kept between solves of one solver
+            dev[keep:].zero_()               # buffers (one of them pinned) are kept between solves of one solver
         else:
-            self._diag_dev = torch.zeros(rows, self._n_metrics, dtype=torch.float64, device=device())
-            self._diag_host = torch.zeros(rows, self._n_metrics, dtype=torch.float64).pin_memory()
+            new_dev = torch.zeros(rows, self._n_metrics, dtype=torch.float64, device=device())
+            new_host = torch.zeros(rows, self._n_metrics, dtype=torch.float64).pin_memory()
+            if keep and dev is not None:
+                n = min(int(keep), dev.shape[0])
+                new_dev[:n].copy_(dev[:n])
+                new_host[:n].copy_(self._diag_host[:n])
+            self._diag_dev, self._diag_host = new_dev, new_host
         self._diag_events = {}
 
     def _post_metric_copy(self, it):
@@ -83,10 +96,13 @@ class _DeviceLoop:
     def _rel(dss, ss):
         return np.inf if ss == 0 else float(np.sqrt(dss) / np.sqrt(ss))
 
-    def _run_loop(self, state):
-        """Reference loop ``core/solver.py:64-76`` with a one-deep speculative update.  Returns the final state."""
-        self._alloc_diag()
-        it = 0
+    def _run_loop(self, state, it0=0):
+        """Reference loop ``core/solver.py:64-76`` with a one-deep speculative update.  Returns the final state.
+
+        ``it0``: the update count to continue from -- as in the reference, a second ``iterate()`` without ``reset()``
+        carries on at ``self.iter`` (and does nothing if the loop condition already fails)."""
+        self._alloc_diag(keep=it0)
+        it = int(it0)
         spec = None                          # speculative (state, it) already launched for index `it`
         while True:
             # Updates up to min_iter run unconditionally (core/solver.py:65-66): a plan that can enqueue several updates
@@ -342,9 +358,9 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
         return self._plan
 
     # -- slab decomposition: the norms of the stop test are per-rank partial sums until all-reduced ----------------
-    def _alloc_diag(self):
-        super()._alloc_diag()
-        self._diag_reduced = set()
+    def _alloc_diag(self, keep=0):
+        super()._alloc_diag(keep)
+        self._diag_reduced = set(range(int(keep)))
 
     def _post_metric_copy(self, it):
         if self._slab is not None and it not in self._diag_reduced:
@@ -374,8 +390,9 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
 
     def iterate(self) -> Any:
         self._make_plan()
-        state = self._init_state() if self.iter == 0 or self.iterand is None else self._state_from_iterand()
-        x, z = self._run_loop(state)
+        fresh = self.iter == 0 or self.iterand is None
+        state = self._init_state() if fresh else self._state_from_iterand()
+        x, z = self._run_loop(state, 0 if fresh else self.iter)
         self.converged = True
         if self._slab is not None:
             self._plan.check()
@@ -384,35 +401,63 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
             self._plan.release(x, z)
         self._state = (x, z)
         self.iterand = {'primal_variable': self._as_output(x), 'dual_variable': self._as_output(z)}
+        self._cont = None if self._slab is not None else (self.iterand, (x, z))
         self.old_iterand = self.iterand
         self.diagnostics = self._build_diagnostics(self.iter)
         return self.iterand, self.converged, self.diagnostics
 
-    def _state_from_iterand(self):
+    def _state_from_iterand(self, for_write=True):
+        """Device state to continue from ``self.iterand``.  ``for_write``: the caller may overwrite the state buffers
+        (the multi-update path ping-pongs into them), so tensors the user can see are copied first."""
         it = self.iterand
+        cont = getattr(self, '_cont', None)
+        if cont is not None and cont[0] is it:          # the iterand this solver produced last: its device state is kept
+            x, z = cont[1]
+            if for_write and self._slab is None and isinstance(it['primal_variable'], torch.Tensor):
+                x, z = x.clone(), (None if z is None else z.clone())
+            return x, z
         if self._slab is not None:
             return self._plan.init_state(it['primal_variable'], it['dual_variable'])
-        x = to_device(it['primal_variable'], self._dtype)
-        z = None if it['dual_variable'] is None else to_device(it['dual_variable'], self._dtype)
+        # a caller-owned iterand: private copies (the multi-update path writes into its state buffers)
+        x = _own_copy(it['primal_variable'], self._dtype)
+        z = None if it['dual_variable'] is None else _own_copy(it['dual_variable'], self._dtype)
         return x, z
 
     def update_iterand(self) -> dict:
-        """One update on the current iterand (used by ``iterates(n)``); returns device tensors."""
+        """One update on the current iterand (used by ``iterates(n)``, core/solver.py:88-103).
+
+        As in the reference every call returns FRESH arrays (numpy unless the solver was given device tensors / ``output=
+        'torch'``): the buffers of a fused plan are handed over to the caller, never recycled under a yielded iterate."""
         if self._slab is not None:
-            raise NotImplementedError('iterates(n) / update_iterand() are not available in slab mode; use iterate()')
+            self._make_plan()
+            if self.iter == 0 or self.iterand is None:
+                x, z = self._plan.init_state(self._user_x0, self._user_z0)
+            else:
+                x, z = self._state_from_iterand(for_write=False)
+            if not hasattr(self, '_scratch_row'):
+                self._scratch_row = torch.zeros(self._n_metrics, dtype=torch.float64, device=device())
+            x, z = self._plan.step(x, z, self._scratch_row)
+            self._plan.check()
+            xo, zo = self._plan.extract(x, z)             # fresh copies of this rank's rows
+            out = {'primal_variable': self._as_output(xo), 'dual_variable': self._as_output(zo)}
+            self._cont = (out, (x, z))
+            return out
         if self._plan is None and self._allow_fused:
             self._make_plan()
         if self.iter == 0 or self.iterand is None:
             x, z = self._init_state()
         else:
-            x, z = self._state_from_iterand()
+            x, z = self._state_from_iterand(for_write=False)
         if not hasattr(self, '_scratch_row'):
             self._scratch_row = torch.zeros(self._n_metrics, dtype=torch.float64, device=device())
         if self._plan is not None:
             x, z = self._plan.step(x, z, self._scratch_row)
+            self._plan.release(x, z)
         else:
             x, z = self._generic_step(x, z, self._scratch_row)
-        return {'primal_variable': x, 'dual_variable': z}
+        out = {'primal_variable': self._as_output(x), 'dual_variable': self._as_output(z)}
+        self._cont = (out, (x, z))
+        return out
 
     # -- resumability (SURVEY.md 8(f) rank 4): the state of a solve is (x, z, tau, sigma, rho) ------------------------
     def save_checkpoint(self, path: str):
@@ -584,18 +629,20 @@ class AcceleratedProximalGradientDescent(_DeviceLoop, GenericIterativeAlgorithm)
 
     def iterate(self) -> Any:
         self._make_plan()
-        if self.iter == 0 or self.iterand is None:
+        fresh = self.iter == 0 or self.iterand is None
+        if fresh:
             state = self._init_state()
         else:
             state = (to_device(self.iterand['iterand'], self._dtype), to_device(self.iterand['past_aux'], self._dtype),
                      self.iterand['past_t'])
+        it0 = 0 if fresh else int(self.iter)         # a second iterate() without reset() continues (core/solver.py:64-66)
         if self._plan is not None and hasattr(self._plan, 'run') and self.verbose is None:
             # the whole loop -- updates, norms and the reference's stop test -- runs inside one kernel
-            self._alloc_diag()
-            x, aux, t, self.iter = self._plan.run(state[0], state[1], state[2], self.iter, self._diag_dev)
+            self._alloc_diag(keep=it0)
+            x, aux, t, self.iter = self._plan.run(state[0], state[1], state[2], it0, self._diag_dev[it0:])
             self._diag_host[:self.iter].copy_(self._diag_dev[:self.iter])
         else:
-            x, aux, t = self._run_loop(state)
+            x, aux, t = self._run_loop(state, it0)
         self.converged = True
         self.iterand = {'iterand': self._as_output(x), 'past_aux': self._as_output(aux), 'past_t': t}
         self.old_iterand = self.iterand
@@ -605,8 +652,11 @@ class AcceleratedProximalGradientDescent(_DeviceLoop, GenericIterativeAlgorithm)
     def update_iterand(self) -> Any:
         if self._plan is None and self._allow_fused:
             self._make_plan()
+        cont = getattr(self, '_cont', None)
         if self.iter == 0 or self.iterand is None:
             x, x_old, t_old = self._init_state()
+        elif cont is not None and cont[0] is self.iterand:      # the iterand this solver yielded last: device state kept
+            x, x_old, t_old = cont[1]
         else:
             x, x_old, t_old = (to_device(self.iterand['iterand'], self._dtype),
                                to_device(self.iterand['past_aux'], self._dtype), self.iterand['past_t'])
@@ -617,7 +667,10 @@ class AcceleratedProximalGradientDescent(_DeviceLoop, GenericIterativeAlgorithm)
             x, aux, t, _ = self._plan.run(x, x_old, t_old, self.iter, self._scratch_row, single=True)
         else:
             x, aux, t = self._generic_step(x, x_old, t_old, self.iter, self._scratch_row)
-        return {'iterand': x, 'past_aux': aux, 'past_t': t}
+        # fresh arrays every call, numpy unless the solver was given device tensors (core/solver.py:88-103)
+        out = {'iterand': self._as_output(x), 'past_aux': self._as_output(aux), 'past_t': t}
+        self._cont = (out, (x, aux, t))
+        return out
 
     def _diag_row(self, it):
         d = self._diag_host[it]

@@ -208,13 +208,54 @@ def test_iterates_generator_and_torch_output():
     mk = lambda **kw: m['PDS'](dim=N, F=F, H=0.1 * m['L21Norm'](2 * N, np.tile(np.arange(N), 2)), K=tv_K(shape),
                                verbose=None, **kw)
     s = mk()
-    its = [it['primal_variable'].clone() for it in s.iterates(5)]
+    its = [it['primal_variable'] for it in s.iterates(5)]            # numpy in, numpy out (as the reference yields)
+    assert all(isinstance(a, np.ndarray) for a in its)
     s2 = mk(max_iter=4, min_iter=4, accuracy_threshold=0)
     est, _, _ = s2.iterate()
-    assert rel_l2(its[-1].cpu().numpy(), est['primal_variable']) < 1e-14
+    assert rel_l2(its[-1], est['primal_variable']) < 1e-14
     s3 = mk(max_iter=4, min_iter=4, accuracy_threshold=0, x0=torch.zeros(N, dtype=torch.float64, device='cuda'))
     est3, _, _ = s3.iterate()
     assert isinstance(est3['primal_variable'], torch.Tensor) and est3['primal_variable'].is_cuda
+
+
+@pytest.mark.parametrize('output', ['numpy', 'torch'])
+def test_iterates_yield_fresh_arrays_and_iterate_continues(output):
+    """core/solver.py:88-103: every yielded iterand is a fresh array (collected WITHOUT copying, they must equal the
+    op-by-op path's iterates one by one); core/solver.py:64-66: a second iterate() without reset() continues at
+    self.iter -- a no-op once iter > max_iter, more updates after max_iter was raised -- and keeps earlier diagnostics."""
+    m = _imports()
+    shape = (40, 136)
+    N = shape[0] * shape[1]
+    _, psf, y = synth.tv_deconv_problem(shape, None, 0.02, 3)
+    F = (1 / 2) * m['SquaredL2Loss'](dim=N, data=y) * m['Convolve2D'](size=N, filter=psf, shape=shape)
+    mk = lambda **kw: m['PDS'](dim=N, F=F, G=m['NonNegativeOrthant'](dim=N),
+                               H=0.1 * m['L21Norm'](2 * N, np.tile(np.arange(N), 2)), K=tv_K(shape), beta=1.0,
+                               verbose=None, output=output, **kw)
+    fused, generic = mk(), mk(fused=False)
+    got = list(fused.iterates(6))                       # no .clone(): the plan must not recycle yielded buffers
+    ref = list(generic.iterates(6))
+    assert type(fused._plan).__name__ == 'PdsTvPlan' and generic._plan is None
+    host = (lambda t: t.cpu().numpy()) if output == 'torch' else (lambda a: a)
+    for a, b in zip(got, ref):
+        assert isinstance(a['primal_variable'], np.ndarray if output == 'numpy' else __import__('torch').Tensor)
+        assert rel_l2(host(a['primal_variable']), host(b['primal_variable'])) < 1e-13
+        assert rel_l2(host(a['dual_variable']), host(b['dual_variable'])) < 1e-13
+    assert len({a['primal_variable'].ctypes.data if output == 'numpy' else a['primal_variable'].data_ptr() for a in got}) == 6
+    # continuation
+    s = mk(max_iter=5, min_iter=5, accuracy_threshold=0)
+    est, _, d1 = s.iterate()
+    x6 = host(est['primal_variable']).copy()
+    assert s.iter == 6 and rel_l2(x6, host(got[5]['primal_variable'])) < 1e-13
+    est_b, _, d1b = s.iterate()                          # loop condition already false: nothing happens
+    assert s.iter == 6 and np.array_equal(host(est_b['primal_variable']), x6) and len(d1b) == 6
+    s.max_iter = s.min_iter = 9
+    est2, _, d2 = s.iterate()                            # four more updates, from update 6 on
+    assert s.iter == 10 and len(d2) == 10
+    assert np.array_equal(host(est['primal_variable']), x6)       # the first result was not overwritten
+    full = mk(max_iter=9, min_iter=9, accuracy_threshold=0)
+    estf, _, df = full.iterate()
+    assert rel_l2(host(est2['primal_variable']), host(estf['primal_variable'])) < 1e-13
+    assert np.allclose(d2.to_numpy(dtype=float), df.to_numpy(dtype=float), rtol=1e-9)
 
 
 def _c4_solver(shape, mask, y, lam, eps, k, dtype='complex128', output='numpy', fused=True):
