@@ -22,6 +22,10 @@ extern "C" {
 int pcs_version(void);
 const char* pcs_last_error(void);
 int pcs_num_sms(void);
+/* Planning override of the SM count the launch geometries are sized for (n <= 0: the device's own); returns the
+ * previous override.  Results never depend on it -- the parity tests use it to run the one-wave / uneven-split
+ * geometries of the fused kernels on small images.  Process-wide; not for concurrent use. */
+int pcs_set_num_sms(int n);
 
 #define PCS_DECL_REAL(name, params) int name##_f32 params; int name##_f64 params;
 
@@ -172,6 +176,11 @@ int pcs_mask_indices(const void* mask_u8, int64_t n, const void* workspace, void
  *   warp-specialised one).  diag_out_f64[4] = ||x'-x||^2, ||x||^2, ||z'-z||^2, ||z||^2 (deterministic).
  *   workspace: pcs_pds_tv_workspace_bytes() bytes, zero-initialised once. */
 int64_t pcs_pds_tv_workspace_bytes(void);
+/* What the last pcs_pds_tv_step / _run / _step_slab call of the calling host thread launched (HOST int64[8]):
+ * {kernel (0 single-role, 1 warp-specialised), blocks, threads per block, dynamic shared memory, strips,
+ *  output columns per strip, long segments of the uneven one-wave split (-1: even split), TMA staging used}.
+ * Diagnostic only: the parity tests assert that the benchmarked kernel and geometry are the ones under test. */
+int pcs_pds_tv_last_launch(int64_t* out8_host);
 PCS_DECL_REAL(pcs_pds_tv_step,
               (void* x_out, void* z_out, const void* x, const void* z, const void* b, int64_t H_loc, int64_t W,
                int64_t row_begin, int64_t row_end, int64_t grow0, int64_t Hg, int data_mode, int ntaps,

@@ -1,8 +1,9 @@
 """Import the UNMODIFIED reference ``pycsou`` in the build container.
 
 TEST INFRASTRUCTURE ONLY (see ``oracle/__init__.py``).  Used by ``tests/golden/gen_golden.py`` and
-by the ``needs_reference`` tests to pin ``oracle.np_oracle``.  It is never used on the GPU box
-(``/root/reference`` does not exist there).
+by the ``needs_reference`` tests to pin ``oracle.np_oracle``, and by ``oracle/ref_problems.py`` (the CPU reference arm of
+``bench.py``).  On the GPU box ``/root/reference`` does not exist; the archive ``oracle/_ref/pycsou_reference.zip``
+(``oracle/make_ref.py``; git-ignored, shipped with the snapshot) is used there.
 
 What the shim does:
 
@@ -25,12 +26,35 @@ import types
 
 import numpy as np
 
-REFERENCE_ROOTS = ('/root/reference', os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
-                                                   'baseline', '_ref'))
+_REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+# the live tree (build container); the archive packed by oracle/make_ref.py (travels to the GPU box; imported through
+# zipimport); a driver-made install
+REFERENCE_ROOTS = ('/root/reference', os.path.join(_REPO, 'oracle', '_ref', 'pycsou_reference.zip'),
+                   os.path.join(_REPO, 'baseline', '_ref'))
+
+
+def _has_reference(root: str) -> bool:
+    if os.path.isdir(root):
+        return os.path.isdir(os.path.join(root, 'pycsou', 'opt'))
+    if os.path.isfile(root) and root.endswith('.zip'):
+        import zipfile
+        try:
+            with zipfile.ZipFile(root) as z:
+                return 'pycsou/opt/proxalgs.py' in z.namelist()
+        except zipfile.BadZipFile:
+            return False
+    return False
+
+
+def reference_root():
+    roots = REFERENCE_ROOTS
+    if os.environ.get('PCS_REFERENCE_ROOT'):            # tests: force one root (e.g. the archive while the tree exists)
+        roots = (os.environ['PCS_REFERENCE_ROOT'],)
+    return next((r for r in roots if _has_reference(r)), None)
 
 
 def reference_available() -> bool:
-    return any(os.path.isdir(os.path.join(r, 'pycsou', 'opt')) for r in REFERENCE_ROOTS)
+    return reference_root() is not None
 
 
 def _restore_numpy_aliases():
@@ -93,7 +117,7 @@ def load_reference():
     global _ref
     if _ref is not None:
         return _ref
-    root = next((r for r in REFERENCE_ROOTS if os.path.isdir(os.path.join(r, 'pycsou', 'opt'))), None)
+    root = reference_root()
     if root is None:
         raise ImportError('reference pycsou not present (expected in the build container only)')
     _restore_numpy_aliases()

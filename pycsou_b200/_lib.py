@@ -84,6 +84,7 @@ PLAIN = {
     'pcs_mask_workspace_bytes': ([I64], I64),
     'pcs_reduce_workspace_bytes': ([], I64),
     'pcs_pds_tv_workspace_bytes': ([], I64),
+    'pcs_pds_tv_last_launch': ([P], I32),
     # peer (NVLink) memory for the slab-decomposed solvers (csrc/pcs_peer.cu)
     'pcs_peer_handle_bytes': ([], I32),
     'pcs_peer_alloc': ([P, I64, P], I32),
@@ -102,6 +103,7 @@ PLAIN = {
     'pcs_cps_mri_ball_step_c128': ([P] * 6 + [I64, F64, F64, F64, F64, P, P, P], I32),
     'pcs_version': ([], I32),
     'pcs_num_sms': ([], I32),
+    'pcs_set_num_sms': ([I32], I32),
 }
 
 

@@ -26,7 +26,12 @@ int check_launch(const char* what) {
     return PCS_OK;
 }
 
+// planning override (pcs_set_num_sms): lets the tests drive the one-wave / uneven-split launch geometries of the fused
+// kernels at small image sizes; 0 = the device's own count
+static int g_num_sms_override = 0;
+
 int num_sms() {
+    if (g_num_sms_override > 0) return g_num_sms_override;
     static thread_local int cached_dev = -1, cached = 148;
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return 148;
@@ -45,6 +50,11 @@ using namespace pcs;
 extern "C" int pcs_version(void) { return 100; }
 extern "C" const char* pcs_last_error(void) { return pcs::g_err; }
 extern "C" int pcs_num_sms(void) { return pcs::num_sms(); }
+extern "C" int pcs_set_num_sms(int n) {
+    const int prev = pcs::g_num_sms_override;
+    pcs::g_num_sms_override = n > 0 ? n : 0;
+    return prev;
+}
 
 // ------------------------------------------------------------------------------------------------ elementwise
 constexpr int EW_BLOCK = 256;

@@ -192,7 +192,7 @@ class PdsTvPlan:
                 pack[k, :E.shape[0], :E.shape[1]] = E
             self.nl, self.nr, self.nt, self.nb = El.shape[0], Er.shape[0], Et.shape[0], Eb.shape[0]
             self.edge = to_device(pack.reshape(-1), dt)
-            self.b = A._adjoint(to_device(y, dt))           # A^T y, once per solve
+            self._A, self._y = A, to_device(y, dt)          # A^T y is formed by begin_solve(), once per solve
         nbytes = int(_lib.call_plain('pcs_pds_tv_workspace_bytes'))
         self.ws = torch.zeros(nbytes // 8, dtype=torch.float64, device=dev)
         self._xbuf, self._zbuf = [None, None], [None, None]
@@ -201,6 +201,15 @@ class PdsTvPlan:
         self.use_tma = int(os.environ.get('PCS_PDS_TMA', '1'))
         if self.b is not None and self.b.numel() != H * W:
             raise _NoMatch('data size mismatch')
+        if data_mode == DM_CONV and self._y.numel() != H * W:
+            raise _NoMatch('data size mismatch')
+
+    def begin_solve(self):
+        """Per-solve precomputation: ``b = A^T y`` for the deconvolution problems (the kernel evaluates the data-term
+        gradient as ``(A^T A) x - b``).  Runs at the start of EVERY solve -- part of the solve's cost, and a ``y`` that was
+        modified in place between two solves is honoured."""
+        if self.data_mode == DM_CONV:
+            self.b = self._A._adjoint(self._y)
 
     def _out(self, pool, like):
         for k in (0, 1):
@@ -223,6 +232,8 @@ class PdsTvPlan:
         if self.data_mode == DM_GIVEN:
             b = s.F._gradient(x)
         else:
+            if self.b is None and self.data_mode == DM_CONV:
+                self.begin_solve()
             b = self.b
         xo, zo = self._out(self._xbuf, x), self._out(self._zbuf, z)
         crow = self.crow.ctypes.data_as(C.c_void_p) if self.crow is not None else None
@@ -235,9 +246,21 @@ class PdsTvPlan:
         return xo, zo
 
 
+def last_launch():
+    """Kernel and launch geometry of this thread's last fused Condat-Vu update (``pcs_pds_tv_last_launch``)."""
+    out = np.zeros(8, dtype=np.int64)
+    _lib.check(_lib.call_plain('pcs_pds_tv_last_launch', out.ctypes.data_as(C.c_void_p)))
+    keys = ('kernel', 'blocks', 'threads', 'smem', 'strips', 'strip_cols', 'n_fast', 'use_tma')
+    d = dict(zip(keys, (int(v) for v in out)))
+    d['kernel'] = {0: 'pds_tv_kernel', 1: 'pds_tv_ws_kernel'}.get(d['kernel'], 'none')
+    return d
+
+
 def _run_many(self, x, z, n, drows):
     """``n`` consecutive updates enqueued by ONE library call (``pcs_pds_tv_run``); ``drows``: n x 4 diagnostics rows."""
     s = self.solver
+    if self.b is None and self.data_mode == DM_CONV:
+        self.begin_solve()
     xo, zo = self._out(self._xbuf, x), self._out(self._zbuf, z)
     crow = self.crow.ctypes.data_as(C.c_void_p) if self.crow is not None else None
     ccol = self.ccol.ctypes.data_as(C.c_void_p) if self.ccol is not None else None

@@ -391,6 +391,8 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
     def iterate(self) -> Any:
         self._make_plan()
         fresh = self.iter == 0 or self.iterand is None
+        if fresh and hasattr(self._plan, 'begin_solve'):
+            self._plan.begin_solve()                  # per-solve precomputation (A^T y), inside the solve
         state = self._init_state() if fresh else self._state_from_iterand()
         x, z = self._run_loop(state, 0 if fresh else self.iter)
         self.converged = True

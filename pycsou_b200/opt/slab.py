@@ -136,12 +136,19 @@ def gather_halo(own: torch.Tensor, above: int, below: int, rank: int, world: int
 class SlabComm:
     """The process group a slab-decomposed solve runs on (default: the world group)."""
 
-    def __init__(self, group=None):
+    def __init__(self, group=None, lockstep=None):
+        """``lockstep``: complete every update on all ranks before any rank launches the next one (a device
+        synchronisation and a barrier per update).  The update kernels of neighbouring ranks hand over through flag
+        words and SPIN until the neighbour's previous update has been published, which is only safe when the ranks
+        really run concurrently, one per GPU.  Ranks that share a GPU (the single-GPU test set-up: gloo control plane,
+        CUDA IPC between processes on one device) are time-sliced, so a spinning kernel could starve the kernel it
+        waits for; in lockstep no kernel ever has to wait.  Default: on exactly when the backend is gloo."""
         if not dist.is_initialized():
             raise RuntimeError('SlabComm needs an initialised torch.distributed process group')
         self.group = group
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
+        self.lockstep = (dist.get_backend(group) == 'gloo') if lockstep is None else bool(lockstep)
 
     def layout(self, Hg: int, W: int) -> SlabLayout:
         return SlabLayout(Hg, W, self.world, self.rank)
@@ -313,14 +320,10 @@ class SlabPdsTvPlan:
             if y_own.numel() != lay.n_own * W:
                 raise ValueError(f'slab mode: the data must hold this rank\'s {lay.n_own} rows ({lay.n_own * W} values), '
                                  f'got {y_own.numel()}')
-            y_own = y_own.view(lay.n_own, W)
+            self._y_own = y_own.view(lay.n_own, W)
+            self._A = A
             self.b = torch.zeros(lay.plane, dtype=dt, device=dev)
-            bv = self.b.view(lay.H_loc, W)
-            if data_mode == Fz.DM_IDENTITY:
-                ext = gather_halo(y_own, 0, 1, comm.rank, comm.world, comm.group)
-                bv[lay.row_begin:lay.row_begin + ext.shape[0]] = ext
-            else:
-                from ..linop.conv import Convolve2D
+            if data_mode == Fz.DM_CONV:
                 ccol, Et, Eb = Fz.composite_filter(A.hcol, A.offset[0])
                 crow, El, Er = Fz.composite_filter(A.hrow, A.offset[1])
                 n = max(ccol.size, crow.size)
@@ -339,14 +342,7 @@ class SlabPdsTvPlan:
                     pack[k, :E.shape[0], :E.shape[1]] = E
                 self.nl, self.nr, self.nt, self.nb = El.shape[0], Er.shape[0], Et.shape[0], Eb.shape[0]
                 self.edge = to_device(pack.reshape(-1), dt)
-                # A^T y on the rows [r0, r1]: y with Y_UP rows above / Y_DN below, filtered with the zero boundary (the
-                # true one at the image edge), keeping the rows at least Y_UP away from a cut
-                ext = gather_halo(y_own, Y_UP, Y_DN, comm.rank, comm.world, comm.group).contiguous()
-                A_loc = Convolve2D(size=ext.numel(), filter=A.filter, shape=tuple(ext.shape))
-                bt = A_loc._adjoint(ext.reshape(-1)).view(ext.shape)
-                skip = Y_UP if comm.rank > 0 else 0
-                keep = lay.n_own + (1 if comm.rank < comm.world - 1 else 0)
-                bv[lay.row_begin:lay.row_begin + keep] = bt[skip:skip + keep]
+            self._b_ready = False
         nbytes = int(_lib.call_plain('pcs_pds_tv_workspace_bytes'))
         self.ws = torch.zeros(nbytes // 8, dtype=torch.float64, device=dev)
         self.err = torch.zeros(4, dtype=torch.int32, device=dev)
@@ -354,6 +350,29 @@ class SlabPdsTvPlan:
         self._K = K
         self._static_desc()
         comm.barrier()
+
+    def begin_solve(self):
+        """Per-solve precomputation (collective: one halo exchange of ``y``): the data term on the local rows
+        ``[row_begin, row_end]`` -- ``y`` itself, or ``A^T y`` for the deconvolution problems."""
+        from . import _fused as Fz
+        if self.data_mode == Fz.DM_NONE:
+            return
+        lay, comm, W = self.lay, self.comm, self.lay.W
+        bv = self.b.view(lay.H_loc, W)
+        if self.data_mode == Fz.DM_IDENTITY:
+            ext = gather_halo(self._y_own, 0, 1, comm.rank, comm.world, comm.group)
+            bv[lay.row_begin:lay.row_begin + ext.shape[0]] = ext
+        else:
+            # A^T y on the rows [r0, r1]: y with Y_UP rows above / Y_DN below, filtered with the zero boundary (the
+            # true one at the image edge), keeping the rows at least Y_UP away from a cut
+            from ..linop.conv import Convolve2D
+            ext = gather_halo(self._y_own, Y_UP, Y_DN, comm.rank, comm.world, comm.group).contiguous()
+            A_loc = Convolve2D(size=ext.numel(), filter=self._A.filter, shape=tuple(ext.shape))
+            bt = A_loc._adjoint(ext.reshape(-1)).view(ext.shape)
+            skip = Y_UP if comm.rank > 0 else 0
+            keep = lay.n_own + (1 if comm.rank < comm.world - 1 else 0)
+            bv[lay.row_begin:lay.row_begin + keep] = bt[skip:skip + keep]
+        self._b_ready = True
 
     # -- peer descriptor (include/pcsb200.h: pcs_pds_tv_step_slab) --------------------------------------------------
     def _static_desc(self):
@@ -410,6 +429,8 @@ class SlabPdsTvPlan:
 
     def step(self, x, z, drow):
         s, lay = self.solver, self.lay
+        if not getattr(self, '_b_ready', True):
+            self.begin_solve()
         cur = 0 if x.data_ptr() == self.xbuf[0].data_ptr() else 1
         xo, zo = self.xbuf[1 - cur], self.zbuf[1 - cur]
         d = self._peer_desc(1 - cur)
@@ -423,6 +444,8 @@ class SlabPdsTvPlan:
                   self.g_b, self.h_mode, self.lam, float(s.tau), float(s.sigma), float(s.rho), self.steps[0],
                   self.steps[1], 0, 0, 1, drow.data_ptr(), self.ws.data_ptr(), K.stream(),
                   d.ctypes.data_as(C.c_void_p))
+        if self.comm.lockstep and self.comm.world > 1:
+            self.comm.barrier()                      # device synchronisation + barrier: see SlabComm.__init__
         return xo, zo
 
     def check(self):

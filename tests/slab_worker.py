@@ -29,6 +29,9 @@ def main():
     ap.add_argument('--dtype', default='f64')
     ap.add_argument('--data', default='conv', choices=['conv', 'identity'])
     ap.add_argument('--threshold', type=float, default=0.0)
+    ap.add_argument('--check-single', action='store_true',
+                    help='large images: instead of saving the iterates, every rank also solves the WHOLE image alone '
+                         '(single-GPU kernel path) and saves how its rows of the slab solve differ from it')
     a = ap.parse_args()
     rank, world = int(os.environ['RANK']), int(os.environ['WORLD_SIZE'])
     dev = int(os.environ.get('LOCAL_RANK', '0')) if a.backend == 'nccl' else 0
@@ -64,6 +67,22 @@ def main():
         pds = PDS(dim=N, F=F, G=NonNegativeOrthant(dim=N), H=H, K=K, beta=1.0, verbose=None, dtype=tdt, slab=comm,
                   output='numpy', **kw)
         est, _, diag = pds.iterate()
+        if a.check_single:
+            Fw = (1 / 2) * SquaredL2Loss(dim=N, data=y.reshape(-1))
+            if a.data == 'conv':
+                Fw = Fw * Convolve2D(size=N, filter=psf, shape=(Hg, W))
+            whole = PDS(dim=N, F=Fw, G=NonNegativeOrthant(dim=N), H=H, K=K, beta=1.0, verbose=None, dtype=tdt,
+                        output='numpy', **kw)
+            ref, _, dref = whole.iterate()
+            xr = ref['primal_variable'].reshape(Hg, W)[lay.r0:lay.r1].reshape(-1)
+            zr = ref['dual_variable'].reshape(2, Hg, W)[:, lay.r0:lay.r1].reshape(-1)
+            np.savez(os.path.join(a.out, f'rank{rank}.npz'), rows=np.array([lay.r0, lay.r1]),
+                     x_equal=np.array_equal(est['primal_variable'], xr), z_equal=np.array_equal(est['dual_variable'], zr),
+                     x_maxabs=np.max(np.abs(est['primal_variable'] - xr)), z_maxabs=np.max(np.abs(est['dual_variable'] - zr)),
+                     x_norm=np.linalg.norm(xr), diag=diag.to_numpy(dtype=float), diag_ref=dref.to_numpy(dtype=float),
+                     plan_whole=type(whole._plan).__name__, n_iter=pds.iter)
+            pds._plan.close()
+            return
         est2 = None
         if a.threshold == 0:                      # a second solve on the same plan: epochs and buffers carry over
             pds.reset()

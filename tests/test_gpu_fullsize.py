@@ -1,0 +1,188 @@
+"""GPU parity AT THE BENCHMARKED SIZES and on the benchmarked launch geometries (BASELINE.json configs 2-4).
+
+The small-image tests never reach the code the headline numbers come from: at 4096^2 the fused Condat-Vu kernel runs a
+ONE-WAVE grid of two CTAs per SM (33 strips x 9 segments), fp32 deconvolution runs the warp-specialised kernel with the
+``%smid`` companion search and the uneven long/short segment split, and 1024^2 runs through the multi-update entry
+point.  Here the same problems ``bench.py`` times are solved for a few updates on the numpy oracle (the reference's
+algorithm, ``/root/reference/pycsou/opt/proxalgs.py:343-355`` driven by ``core/solver.py:64-76``) and on the GPU:
+
+* fp64 iterates within 1e-10 relative L2 (north_star); fp32 objective within 1e-4 relative; masks bit-exact;
+* the launch that ran is asserted to be the benchmarked one (``pcs_pds_tv_last_launch``).
+
+``pcs_set_num_sms`` additionally drives the one-wave / uneven-split geometry on a small image, where it must not change
+a single bit of the fp64 iterates.
+"""
+import numpy as np
+import pytest
+
+from oracle import np_oracle as O
+from pycsou_b200.util import synth
+from tests.helpers import rel_l2
+
+pytestmark = pytest.mark.gpu
+SQRT8 = np.sqrt(8.)
+LAM3 = 0.02
+
+
+def _mods():
+    from pycsou_b200.func.loss import SquaredL2Loss
+    from pycsou_b200.func.penalty import L21Norm, NonNegativeOrthant, tv_groups
+    from pycsou_b200.linop.conv import Convolve2D
+    from pycsou_b200.linop.diff import Gradient
+    from pycsou_b200.opt._fused import last_launch
+    from pycsou_b200.opt.proxalgs import PDS
+    return locals()
+
+
+def _tv_K(m, shape, dtype):
+    K = m['Gradient'](shape=shape, kind='forward', dtype=dtype)
+    K.lipschitz_cst = K.diff_lipschitz_cst = SQRT8
+    return K
+
+
+# ---------------------------------------------------------------------------------------------- C3 / north star: 4096^2
+@pytest.fixture(scope='module')
+def c3_oracle():
+    """Five Condat-Vu updates of the 4096^2 TV-deconvolution of bench.py on the numpy oracle (fp64; ~3 s per update)."""
+    size, k = 4096, 5
+    shape, N = (size, size), size * size
+    _, psf, y = synth.tv_deconv_problem(shape, synth.gaussian_psf_2d(15, 2.5), 0.02, seed=0)
+    A = O.Convolve2D(N, psf, shape)
+    Fo = O.HalfSquaredL2Loss(y, A, G_lipschitz=1.0)
+    Ko = O.Gradient(shape, kind='forward')
+    xo, zo, diag, n = O.pds_iterate(N, F=Fo, G=O.NonNegativeOrthant(N), H=LAM3 * O.TVL21Norm(2 * N, N), K=Ko,
+                                    K_lipschitz=SQRT8, beta=1.0, max_iter=k - 1, min_iter=k - 1, accuracy_threshold=0)
+
+    def objective(x):
+        return 0.5 * np.linalg.norm(A.matvec(x) - y) ** 2 + LAM3 * O.TVL21Norm(2 * N, N)(Ko.matvec(x))
+    return dict(shape=shape, N=N, k=k, psf=psf, y=y, x=xo, z=zo, diag=diag, objective=objective)
+
+
+def _c3_solver(m, c, dtype, **kw):
+    N, shape = c['N'], c['shape']
+    A = m['Convolve2D'](size=N, filter=c['psf'], shape=shape, dtype=dtype)
+    F = (1 / 2) * m['SquaredL2Loss'](dim=N, data=c['y'].astype(dtype)) * A
+    H = LAM3 * m['L21Norm'](dim=2 * N, groups=m['tv_groups'](N))
+    return m['PDS'](dim=N, F=F, G=m['NonNegativeOrthant'](dim=N), H=H, K=_tv_K(m, shape, dtype), beta=1.0,
+                    max_iter=c['k'] - 1, min_iter=c['k'] - 1, accuracy_threshold=0, verbose=None, dtype=dtype, **kw)
+
+
+def test_c3_north_star_fp64_4096(c3_oracle):
+    m, c = _mods(), c3_oracle
+    s = _c3_solver(m, c, 'float64')
+    est, _, diag = s.iterate()
+    L = m['last_launch']()
+    # the benchmarked fp64 launch: single-role kernel, TMA staging, 33 strips of 127 columns, one wave of <= 296 CTAs
+    assert type(s._plan).__name__ == 'PdsTvPlan' and s._plan.data_mode == 2
+    assert L['kernel'] == 'pds_tv_kernel' and L['use_tma'] == 1 and L['strips'] == 33 and L['strip_cols'] == 126
+    assert 148 < L['blocks'] <= 296
+    ex, ez = rel_l2(est['primal_variable'], c['x']), rel_l2(est['dual_variable'], c['z'])
+    print(f'4096^2 fp64, {c["k"]} updates: rel-L2 x {ex:.2e}, z {ez:.2e}, launch {L}')
+    assert ex <= 1e-10 and ez <= 1e-10
+    for col in ('Relative Improvement (primal variable)', 'Relative Improvement (dual variable)'):
+        assert np.allclose(np.asarray(diag[col], float)[1:], np.asarray(c['diag'][col], float)[1:], rtol=1e-9)
+
+
+def test_c3_fp32_4096_warp_specialised_uneven_split(c3_oracle):
+    m, c = _mods(), c3_oracle
+    s = _c3_solver(m, c, 'float32')
+    est, _, _ = s.iterate()
+    L = m['last_launch']()
+    # the benchmarked fp32 launch: warp-specialised kernel, one wave, %smid companion search + uneven long/short split
+    assert L['kernel'] == 'pds_tv_ws_kernel' and L['use_tma'] == 1 and L['threads'] == 384
+    assert L['n_fast'] >= 0 and 148 < L['blocks'] <= 296
+    x = est['primal_variable'].astype(np.float64)
+    fo, fg = c['objective'](c['x']), c['objective'](x)
+    ex, ez = rel_l2(x, c['x']), rel_l2(est['dual_variable'], c['z'])
+    print(f'4096^2 fp32, {c["k"]} updates: objective rel {abs(fg - fo) / fo:.2e}, rel-L2 x {ex:.2e}, z {ez:.2e}, launch {L}')
+    assert abs(fg - fo) <= 1e-4 * fo                  # north_star: fp32 within 1e-4 relative error in the objective
+    assert ex <= 2e-5 and ez <= 2e-5
+    # the warp-specialised kernel against the single-role one at full size (same arithmetic, other schedule)
+    import os
+    os.environ['PCS_PDS_TMA'] = '3'
+    try:
+        s2 = _c3_solver(m, c, 'float32')
+        est2, _, _ = s2.iterate()
+        assert m['last_launch']()['kernel'] == 'pds_tv_kernel'
+    finally:
+        del os.environ['PCS_PDS_TMA']
+    assert rel_l2(est2['primal_variable'], est['primal_variable']) <= 2e-6
+
+
+# ---------------------------------------------------------------------------------------------- C2: 1024^2 denoising
+@pytest.mark.parametrize('dtype', ['float64', 'float32'])
+def test_c2_tv_denoise_1024(dtype):
+    m = _mods()
+    shape, k, lam = (1024, 1024), 20, 0.1
+    N = shape[0] * shape[1]
+    _, y = synth.tv_denoise_problem(shape, 0.1, 0)
+    Ko = O.Gradient(shape, kind='forward')
+    xo, zo, dref, _ = O.pds_iterate(N, F=O.HalfSquaredL2Loss(y), H=lam * O.TVL21Norm(2 * N, N), K=Ko, K_lipschitz=SQRT8,
+                                    rho=0.9, max_iter=k - 1, min_iter=k - 1, accuracy_threshold=0)
+    F = (1 / 2) * m['SquaredL2Loss'](dim=N, data=y.astype(dtype))
+    s = m['PDS'](dim=N, F=F, H=lam * m['L21Norm'](dim=2 * N, groups=m['tv_groups'](N)), K=_tv_K(m, shape, dtype),
+                 rho=0.9, max_iter=k - 1, min_iter=k - 1, accuracy_threshold=0, verbose=None, dtype=dtype)
+    assert abs(s.tau - 0.3) < 0.05 and s.tau == s.sigma            # proxalgs.py:286-287 with beta = 1, L = sqrt(8)
+    est, _, diag = s.iterate()
+    L = m['last_launch']()
+    assert L['kernel'] == 'pds_tv_kernel' and L['use_tma'] == 1 and L['strips'] == 9
+    ex, ez = rel_l2(est['primal_variable'], xo), rel_l2(est['dual_variable'], zo)
+    print(f'1024^2 {dtype}, {k} updates: rel-L2 x {ex:.2e}, z {ez:.2e}, launch {L}')
+    if dtype == 'float64':
+        assert ex <= 1e-10 and ez <= 1e-10
+        assert np.allclose(np.asarray(diag.iloc[1:, 1], float), np.asarray(dref.iloc[1:, 1], float), rtol=1e-9)
+    else:
+        def obj(x):
+            return 0.5 * np.linalg.norm(x - y) ** 2 + lam * O.TVL21Norm(2 * N, N)(Ko.matvec(x))
+        fo, fg = obj(xo), obj(est['primal_variable'].astype(np.float64))
+        assert abs(fg - fo) <= 1e-4 * fo and ex <= 2e-5 and ez <= 2e-5
+
+
+# ---------------------------------------------------------------------------------------------- C4: 2048^2 complex64
+def test_c4_csmri_2048_complex64():
+    import bench
+    import torch
+    size, k = 2048, 5
+    N = size * size
+    mask, y, eps = bench.c4_problem(size, 0)
+    xo, zo, _, _ = __import__('tests.oracle_cases', fromlist=['c4']).c4(k, mask, y, shape=(size, size), lam=bench.C4_LAM,
+                                                                      eps=eps)
+    s = bench.c4_solver(size, mask, y.astype(np.complex64), eps, k, 'numpy')
+    est, _, _ = s.iterate()
+    assert type(s._plan).__name__ == 'CpsMriPlan'
+    # sampling indices are bit-exact: the device index list of the Masking operator == numpy's flatnonzero
+    Mop = s.K.linops[0].LinOp1
+    assert np.array_equal(Mop._idx(torch.device('cuda')).cpu().numpy(), np.flatnonzero(mask))
+    ex, ez = rel_l2(est['primal_variable'], xo), rel_l2(est['dual_variable'], zo)
+    print(f'2048^2 complex64 CS-MRI, {k} updates: rel-L2 x {ex:.2e}, z {ez:.2e}')
+    assert est['primal_variable'].dtype == np.complex64
+    assert ex <= 2e-5 and ez <= 2e-5
+
+
+# ---------------------------------------------------------------------------------------------- forced geometries
+@pytest.mark.parametrize('dtype', ['float64', 'float32'])
+@pytest.mark.parametrize('nsm', [3, 4, 7])
+def test_one_wave_uneven_split_geometry_on_a_small_image(dtype, nsm, monkeypatch):
+    """With the SM count overridden (``pcs_set_num_sms``) the planner builds the ONE-WAVE grid of the 4096^2 runs
+    (nsm < blocks <= 2 nsm; strips with one segment more than the others) on a 300 x 600 image, and -- for the
+    warp-specialised fp32 kernel -- the uneven long/short split with the ``pds_assign_rows`` companion search.  Neither
+    may change a single bit of the iterates relative to the default (many short segments) geometry."""
+    from pycsou_b200 import _lib
+    from tests.test_gpu_fused import _problem, _run
+    m = _mods()
+    kw = _problem((300, 600), 'sep', 'nonneg', 'l21', dtype)
+    _, base, _ = _run(kw, 4, True)
+    L0 = m['last_launch']()
+    prev = _lib.call_plain('pcs_set_num_sms', nsm)
+    try:
+        _, est, _ = _run(kw, 4, True)
+        L = m['last_launch']()
+    finally:
+        _lib.call_plain('pcs_set_num_sms', prev)
+    assert L['kernel'] == L0['kernel'] and L['blocks'] != L0['blocks'] and L['blocks'] <= 2 * nsm
+    if dtype == 'float32':
+        assert L['kernel'] == 'pds_tv_ws_kernel'
+        if L['blocks'] > nsm:
+            assert L['n_fast'] >= 0                       # uneven split + companion search were exercised
+    assert np.array_equal(est['primal_variable'], base['primal_variable'])
+    assert np.array_equal(est['dual_variable'], base['dual_variable'])

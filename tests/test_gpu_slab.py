@@ -1,9 +1,11 @@
 """GPU parity of the slab-decomposed fused Condat-Vu iteration (csrc/pcs_pds.cu + opt/slab.py) against the numpy oracle.
 
 Ranks are separate processes (tests/slab_worker.py under torch.distributed.run).  On a box with >= 2 GPUs they run one
-per GPU over NCCL and the halo rows travel through NVLink; on a single-GPU box they share cuda:0 (gloo control plane,
-CUDA IPC between the processes), which exercises exactly the same kernel path: peer stores into the neighbour's halo
-rows, release/acquire flag words, all-reduced stop-test norms.
+per GPU over NCCL, free-running: the halo rows travel through NVLink and the kernels of neighbouring ranks hand over
+through the release/acquire flag words.  On a single-GPU box they share cuda:0 (gloo control plane, CUDA IPC between
+the processes) in LOCKSTEP (SlabComm.lockstep: every update is completed on all ranks before the next is launched), so
+that no kernel ever spins on a flag another time-sliced process has yet to write; the kernel path is the same: peer
+stores into the neighbour's halo rows, flag words, all-reduced stop-test norms.
 """
 import os
 import socket
@@ -91,3 +93,19 @@ def test_slab_fp32_objective(tmp_path):
     parts = _run_ranks(2, tmp_path, ['--rows', str(rows), '--cols', str(cols), '--iters', str(iters), '--dtype', 'f32'])
     xo, zo, _, _ = _oracle(rows, cols, iters, 'conv')
     _check(parts, xo, zo, 2e-5)
+
+
+@pytest.mark.parametrize('dtype', ['f64', 'f32'])
+def test_slab_full_size_equals_single_gpu(dtype, tmp_path):
+    """Two 2048 x 4096 slabs of one 4096^2 TV-deconvolution (the benchmarked size and launch geometry of a slab) against
+    the whole image on one GPU: the fp64 iterates must be IDENTICAL on every pixel, fp32 to rounding of the different
+    strip / segment geometry (the kernels are deterministic; only the all-reduced norms differ in summation order)."""
+    parts = _run_ranks(2, tmp_path, ['--rows', '4096', '--cols', '4096', '--iters', '6', '--dtype', dtype, '--check-single'])
+    assert [tuple(d['rows']) for d in parts] == [(0, 2048), (2048, 4096)]
+    for d in parts:
+        assert str(d['plan_whole']) == 'PdsTvPlan' and int(d['n_iter']) == 6
+        if dtype == 'f64':
+            assert bool(d['x_equal']) and bool(d['z_equal']), (float(d['x_maxabs']), float(d['z_maxabs']))
+        else:
+            assert float(d['x_maxabs']) <= 2e-6 and float(d['z_maxabs']) <= 2e-6
+        assert np.allclose(d['diag'][:, 1:], d['diag_ref'][:, 1:], rtol=1e-9 if dtype == 'f64' else 1e-4)
