@@ -3,8 +3,8 @@ r"""Operator glue (mirror of the hot-path part of ``pycsou/linop/base.py``).
 In scope: ``DiagonalOperator, IdentityOperator, NullOperator, HomothetyMap,
 LinOpStack / LinOpVStack / LinOpHStack`` plus a minimal ``DenseLinearOperator`` (plain library GEMV through
 ``torch.mv`` -- explicit-matrix algebra is not part of the stencil path, it exists so that the reference's LASSO
-example runs) and ``PolynomialLinearOperator``.  Sparse / dask / Kronecker / Khatri-Rao / Block operators are out of
-scope and raise.
+example runs), ``PolynomialLinearOperator`` and a duck-typed ``PyLopLinearOperator``.  Sparse / dask /
+Kronecker / Khatri-Rao / Block operators are out of scope and raise.
 """
 from __future__ import annotations
 
@@ -241,7 +241,42 @@ def _out_of_scope(name):
     return ctor
 
 
-PyLopLinearOperator = _out_of_scope('PyLopLinearOperator')
+class PyLopLinearOperator(LinearOperator):
+    r"""Linear operator from a pylops-style object (reference ``linop/base.py:24-54``).
+
+    The reference wraps a ``pylops.LinearOperator`` and forwards ``__call__`` / ``adjoint`` to its ``matvec`` /
+    ``rmatvec`` on numpy arrays.  pylops' own operators are CPU objects (and pylops is not a dependency of this package),
+    so here the adapter is duck-typed: ``PyLop`` is ANY object with ``shape``, ``matvec`` and ``rmatvec`` that maps 1-D
+    **CUDA tensors** to CUDA tensors (``dtype`` and ``explicit`` are read when present).  That is the hook through which
+    user-written device operators enter the solvers of ``pycsou_b200.opt.proxalgs``; an object that returns host arrays
+    is refused (there is no CPU path).
+    """
+
+    def __init__(self, PyLop, is_symmetric: bool = False, is_dense: bool = False, is_sparse: bool = False,
+                 lipschitz_cst: float = np.inf):
+        for attr in ('shape', 'matvec', 'rmatvec'):
+            if not hasattr(PyLop, attr):
+                raise TypeError(f'PyLop must expose shape, matvec and rmatvec (missing {attr})')
+        dt = np.dtype(getattr(PyLop, 'dtype', None) or np.float64)
+        super(PyLopLinearOperator, self).__init__(shape=tuple(PyLop.shape), dtype=dt,
+                                                  is_explicit=bool(getattr(PyLop, 'explicit', False)),
+                                                  is_dense=is_dense, is_sparse=is_sparse, is_dask=False,
+                                                  is_symmetric=is_symmetric, lipschitz_cst=lipschitz_cst)
+        self.Op = PyLop
+
+    @staticmethod
+    def _dev(out, what):
+        if not (isinstance(out, torch.Tensor) and out.is_cuda):
+            raise TypeError(f'PyLopLinearOperator: {what} must return a CUDA tensor (pycsou_b200 has no CPU path)')
+        return out.reshape(-1).contiguous()
+
+    def _apply(self, x):
+        return self._dev(self.Op.matvec(x), 'matvec')
+
+    def _adjoint(self, y):
+        return self._dev(self.Op.rmatvec(y), 'rmatvec')
+
+
 SparseLinearOperator = _out_of_scope('SparseLinearOperator')
 DaskLinearOperator = _out_of_scope('DaskLinearOperator')
 BlockOperator = _out_of_scope('BlockOperator')

@@ -184,6 +184,7 @@ def test_prox_and_projections(dtype, tol):
 
 def test_l21norm_reference_doctest_pin():
     """The reference's own doctest for L21Norm (/root/reference/pycsou/func/penalty.py:494-509): two groups of five."""
+    from pycsou_b200.func import penalty as P
     x = np.arange(10, dtype=np.float64)
     groups = np.concatenate((np.ones(5), 2 * np.ones(5)))
     f = P.L21Norm(dim=x.size, groups=groups)
@@ -203,6 +204,7 @@ def test_l21norm_reference_doctest_pin():
 def test_l21norm_general_groups(dtype, tol):
     """Arbitrary label arrays (penalty.py:532-560): ragged groups, groups longer than a warp, labels in any order,
     a zero group (1 - tau/0 -> -inf -> 0), complex input."""
+    from pycsou_b200.func import penalty as P
     r = rng(11)
     n = 5000
     labels = r.integers(0, 37, size=n).astype(np.float64) * 1.5 - 3        # ragged, unordered, non-integer labels
