@@ -158,6 +158,18 @@ PCS_DECL_REAL(pcs_pool_adj, (void* out, const void* y, int64_t d0, int64_t d1, i
 int64_t pcs_mask_workspace_bytes(int64_t n);
 int pcs_mask_count(const void* mask_u8, int64_t n, void* workspace, void* total_out_i64, void* stream);
 int pcs_mask_indices(const void* mask_u8, int64_t n, const void* workspace, void* idx_out_i64, void* stream);
+/* Allocation-free variant of the pair above.  NO counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * One call = count + scan + write; the chunk counts live in a file-scope `static __device__` array inside the library
+ * (128 KiB per GPU that loads the library, held until exit) instead of a caller workspace, so the call allocates nothing.
+ *   n <= pcs_mask_static_max_n() = 67 108 864 mask entries (an 8192^2 mask); larger masks are rejected (status 1).
+ *   total_out_i64: device int64 <- popcount(mask).  idx_out_i64: device int64[idx_capacity] <- the first
+ *   min(total, idx_capacity) sorted positions (never written beyond idx_capacity; size it n, or a known count).
+ * All calls on a device share the one scratch array: calls that may overlap on the GPU (different streams) race --
+ * serialise them.  Nothing in it has to be cleared between calls (every word read is first written by the same call). */
+int64_t pcs_mask_static_max_n(void);
+int pcs_mask_to_indices_static(const void* mask_u8, int64_t n, void* total_out_i64, void* idx_out_i64,
+                               int64_t idx_capacity, void* stream);
 
 /* ---- fused Condat-Vu (PDS) total-variation iteration: one launch = PrimalDualSplitting.update_iterand +
  *      update_diagnostics (pycsou/opt/proxalgs.py:343-394) for

@@ -82,6 +82,8 @@ PLAIN = {
     'pcs_mask_count': ([P, I64, P, P, P], I32),
     'pcs_mask_indices': ([P, I64, P, P, P], I32),
     'pcs_mask_workspace_bytes': ([I64], I64),
+    'pcs_mask_static_max_n': ([], I64),
+    'pcs_mask_to_indices_static': ([P, I64, P, P, I64, P], I32),
     'pcs_reduce_workspace_bytes': ([], I64),
     'pcs_pds_tv_workspace_bytes': ([], I64),
     'pcs_pds_tv_last_launch': ([P], I32),

@@ -7,6 +7,7 @@
 //
 // (outer, n, inner) view for Restriction along an axis: out[o, j, k] = x[o, idx[j], k].
 #include "pcs_common.cuh"
+#include <mutex>
 
 using namespace pcs;
 
@@ -168,6 +169,86 @@ extern "C" int pcs_mask_indices(const void* mask_u8, int64_t n, const void* work
     mask_write_kernel<<<(unsigned)((nchunks + warps - 1) / warps), SG_BLOCK, 0, (cudaStream_t)stream>>>(
         (const uint8_t*)mask_u8, n, (const int64_t*)workspace, (int64_t*)idx_out_i64);
     return check_launch("pcs_mask_indices");
+}
+
+// ---- allocation-free variant ------------------------------------------------------------------------------------------
+// pcs_mask_to_indices_static: mask -> count + sorted positions in ONE call that allocates nothing (no cudaMalloc / cudaFree,
+// no allocating library routine): for callers under CUDA graph capture, tight serving loops and harnesses that forbid
+// allocation.  The per-chunk counts / offsets that pcs_mask_count keeps in a caller-provided workspace live in a
+// file-scope device array instead (one copy per GPU that loads the library, held until exit), which bounds the mask size:
+// n <= PCS_MASK_STATIC_MAX_N = MK_STATIC_MAX_CHUNKS * MK_CHUNK = 64 Mi entries (an 8192^2 mask); 128 KiB of scratch.
+// No counterpart in the reference.
+constexpr int64_t MK_STATIC_MAX_CHUNKS = 16384;
+static __device__ __align__(256) unsigned char g_mask_static_scratch[(MK_STATIC_MAX_CHUNKS + 2) * 8];
+
+// as mask_write_kernel, but never writes beyond `capacity` entries (the caller sizes idx_out without a host read-back)
+__global__ void mask_write_capped_kernel(const uint8_t* __restrict__ mask, int64_t n, const int64_t* __restrict__ offsets,
+                                         int64_t* __restrict__ idx, int64_t capacity) {
+    const int lane = threadIdx.x & 31;
+    const int64_t chunk = (int64_t)blockIdx.x * (SG_BLOCK / 32) + (threadIdx.x >> 5);
+    const int64_t base = chunk * MK_CHUNK;
+    if (base >= n) return;
+    int64_t pos = offsets[chunk];
+    for (int e = 0; e < MK_CHUNK; e += 32) {
+        const int64_t i = base + e + lane;
+        const bool set = (i < n) && mask[i];
+        const unsigned b = __ballot_sync(0xffffffffu, set);
+        const int64_t o = pos + __popc(b & ((1u << lane) - 1u));
+        if (set && o < capacity) idx[o] = i;
+        pos += __popc(b);
+    }
+}
+
+// Device address of the scratch array ON THE CURRENT DEVICE.  In host code the array's name is only a host-side stand-in
+// (not a device address): the address comes from cudaGetSymbolAddress, looked up once per device with that device current.
+static int mask_static_scratch_ptr(int64_t** out) {
+    constexpr int MAXDEV = 64;
+    static void* cache[MAXDEV] = {nullptr};
+    static std::mutex mu;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAXDEV) {
+        set_error("pcs_mask_to_indices_static: cannot identify the current device");
+        return PCS_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (cache[dev] == nullptr) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_mask_static_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            set_error("pcs_mask_to_indices_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+            return PCS_ERR_CUDA;
+        }
+        cache[dev] = p;
+    }
+    *out = (int64_t*)cache[dev];
+    return PCS_OK;
+}
+
+extern "C" int64_t pcs_mask_static_max_n(void) { return MK_STATIC_MAX_CHUNKS * (int64_t)MK_CHUNK; }
+
+extern "C" int pcs_mask_to_indices_static(const void* mask_u8, int64_t n, void* total_out_i64, void* idx_out_i64,
+                                          int64_t idx_capacity, void* stream) {
+    PCS_REQUIRE(n >= 0 && idx_capacity >= 0 && total_out_i64 && (n == 0 || mask_u8) && (idx_capacity == 0 || idx_out_i64),
+                "pcs_mask_to_indices_static: bad arguments");
+    PCS_REQUIRE(n <= pcs_mask_static_max_n(),
+                "pcs_mask_to_indices_static: mask of %lld entries exceeds the static scratch limit of %lld entries "
+                "(use pcs_mask_count / pcs_mask_indices with a caller-provided workspace)",
+                (long long)n, (long long)pcs_mask_static_max_n());
+    int64_t* scratch = nullptr;
+    const int rc = mask_static_scratch_ptr(&scratch);
+    if (rc != PCS_OK) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t nchunks = (n + MK_CHUNK - 1) / MK_CHUNK;
+    // every word of the scratch this call reads is written by this call first (counts[0 .. nchunks) by the count kernel,
+    // turned into offsets by the scan): nothing has to start at zero, stale contents of earlier calls are never read
+    if (nchunks > 0) mask_count_kernel<<<(unsigned)nchunks, SG_BLOCK, 0, s>>>((const uint8_t*)mask_u8, n, scratch);
+    mask_scan_kernel<<<1, 32, 0, s>>>(scratch, nchunks, (int64_t*)total_out_i64);
+    if (nchunks > 0 && idx_capacity > 0) {
+        const int warps = SG_BLOCK / 32;
+        mask_write_capped_kernel<<<(unsigned)((nchunks + warps - 1) / warps), SG_BLOCK, 0, s>>>(
+            (const uint8_t*)mask_u8, n, scratch, (int64_t*)idx_out_i64, idx_capacity);
+    }
+    return check_launch("pcs_mask_to_indices_static");
 }
 
 // ------------------------------------------------------------------------------------------------ block pooling
