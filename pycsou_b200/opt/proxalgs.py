@@ -462,23 +462,41 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
         return out
 
     # -- resumability: the state of a solve is (x, z, tau, sigma, rho) ------------------------
+    def _ckpt_path(self, path: str) -> str:
+        """Slab mode: one file per rank (``<path>.rank<r>of<world>``), each holding that rank's rows."""
+        if self._slab is None:
+            return path
+        return f'{path}.rank{self._slab.rank}of{self._slab.world}'
+
     def save_checkpoint(self, path: str):
-        """Write the current iterates and step sizes to ``path`` (``torch.save``); single-GPU solvers."""
-        if self._slab is not None:
-            raise NotImplementedError('checkpoints of slab-decomposed solves: save each rank\'s iterand')
+        """Write the current iterates and step sizes (``torch.save``).  Slab-decomposed solves (every rank calls it):
+        each rank writes ITS rows of ``x`` and of both planes of ``z`` to ``<path>.rank<r>of<world>`` -- a 32768^2 solve
+        never gathers its state on one rank."""
         if getattr(self, '_state', None) is None:
             raise RuntimeError('nothing to checkpoint: call iterate() first')
         x, z = self._state
-        torch.save({'primal_variable': x.cpu(), 'dual_variable': None if z is None else z.cpu(), 'updates': int(self.iter),
-                    'tau': float(self.tau), 'sigma': None if self.sigma is None else float(self.sigma),
-                    'rho': float(self.rho), 'dim': int(self.dim)}, path)
+        ck = {'primal_variable': x.cpu(), 'dual_variable': None if z is None else z.cpu(), 'updates': int(self.iter),
+              'tau': float(self.tau), 'sigma': None if self.sigma is None else float(self.sigma),
+              'rho': float(self.rho), 'dim': int(self.dim)}
+        if self._slab is not None:
+            lay = self._plan.lay
+            ck.update(rows=(int(lay.r0), int(lay.r1)), world=int(self._slab.world), image=(int(lay.Hg), int(lay.W)))
+        torch.save(ck, self._ckpt_path(path))
+        if self._slab is not None:
+            self._slab.barrier()
 
     def load_checkpoint(self, path: str) -> int:
         """Warm-start this solver from a checkpoint: the next ``iterate()`` continues from the saved iterates with the
-        saved step sizes.  Returns the number of updates the checkpointed solve had done."""
-        ck = torch.load(path)
+        saved step sizes.  Returns the number of updates the checkpointed solve had done.  Slab mode: every rank loads
+        its own file; the decomposition (world size, rows) must be the one the checkpoint was written with."""
+        ck = torch.load(self._ckpt_path(path))
         if ck['dim'] != self.dim:
             raise ValueError('checkpoint of a problem of another size')
+        if self._slab is not None:
+            self._make_plan()
+            lay = self._plan.lay
+            if ck.get('world') != self._slab.world or tuple(ck.get('rows', ())) != (lay.r0, lay.r1):
+                raise ValueError('checkpoint written with another slab decomposition')
         self._user_x0, self._user_z0 = ck['primal_variable'], ck['dual_variable']
         self.tau, self.rho = ck['tau'], ck['rho']
         if ck['sigma'] is not None:

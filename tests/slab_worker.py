@@ -29,6 +29,9 @@ def main():
     ap.add_argument('--dtype', default='f64')
     ap.add_argument('--data', default='conv', choices=['conv', 'identity'])
     ap.add_argument('--threshold', type=float, default=0.0)
+    ap.add_argument('--resume', action='store_true',
+                    help='SURVEY 8(f)-4 in slab mode: k1 updates, per-rank checkpoint, k2 more from the checkpoint on a '
+                         'new solver; and the same updates streamed through iterates(n).  Saves both results')
     ap.add_argument('--check-single', action='store_true',
                     help='large images: instead of saving the iterates, every rank also solves the WHOLE image alone '
                          '(single-GPU kernel path) and saves how its rows of the slab solve differ from it')
@@ -66,6 +69,28 @@ def main():
             dict(max_iter=a.iters - 1, min_iter=2, accuracy_threshold=a.threshold)
         pds = PDS(dim=N, F=F, G=NonNegativeOrthant(dim=N), H=H, K=K, beta=1.0, verbose=None, dtype=tdt, slab=comm,
                   output='numpy', **kw)
+        if a.resume:
+            k1, k2 = a.iters // 2, a.iters - a.iters // 2
+
+            def mk(k):
+                return PDS(dim=N, F=F, G=NonNegativeOrthant(dim=N), H=H, K=K, beta=1.0, verbose=None, dtype=tdt, slab=comm,
+                           output='numpy', max_iter=k - 1, min_iter=k - 1, accuracy_threshold=0)
+            s1 = mk(k1)
+            s1.iterate()
+            ck = os.path.join(a.out, 'ck.pt')
+            s1.save_checkpoint(ck)
+            s2 = mk(k2)
+            assert s2.load_checkpoint(ck) == k1
+            est, _, _ = s2.iterate()
+            s3 = mk(a.iters)
+            last, ptrs = None, set()
+            for last in s3.iterates(a.iters):            # streamed: fresh arrays of this rank's rows every update
+                ptrs.add(last['primal_variable'].ctypes.data)
+            np.savez(os.path.join(a.out, f'rank{rank}.npz'), x=est['primal_variable'], z=est['dual_variable'],
+                     rows=np.array([lay.r0, lay.r1]), xi=last['primal_variable'], zi=last['dual_variable'],
+                     ck_exists=os.path.exists(f'{ck}.rank{rank}of{world}'), n_fresh=len(ptrs))
+            s3._plan.close()
+            return
         est, _, diag = pds.iterate()
         if a.check_single:
             Fw = (1 / 2) * SquaredL2Loss(dim=N, data=y.reshape(-1))

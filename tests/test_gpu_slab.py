@@ -109,3 +109,15 @@ def test_slab_full_size_equals_single_gpu(dtype, tmp_path):
         else:
             assert float(d['x_maxabs']) <= 2e-6 and float(d['z_maxabs']) <= 2e-6
         assert np.allclose(d['diag'][:, 1:], d['diag_ref'][:, 1:], rtol=1e-9 if dtype == 'f64' else 1e-4)
+
+
+def test_slab_checkpoint_resume_and_iterates(tmp_path):
+    """SURVEY 8(f)-4 for slab-decomposed solves: 7 updates, per-rank checkpoint files, 7 more on a new solver == 14 updates
+    of the oracle; ``iterates(14)`` streams fresh per-rank arrays and ends on the same iterate."""
+    rows, cols, iters = 192, 200, 14
+    parts = _run_ranks(2, tmp_path, ['--rows', str(rows), '--cols', str(cols), '--iters', str(iters), '--resume'])
+    xo, zo, _, _ = _oracle(rows, cols, iters, 'conv')
+    _check(parts, xo, zo, 1e-10)
+    for d in parts:
+        assert bool(d['ck_exists']) and int(d['n_fresh']) >= 2
+        assert np.array_equal(d['xi'], d['x']) and np.array_equal(d['zi'], d['z'])
