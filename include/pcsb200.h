@@ -265,16 +265,23 @@ PCS_DECL_REAL(pcs_apgd_conv1d_run,
  *      path: this is the partitioned form of PrimalDualSplitting.update_iterand, opt/proxalgs.py:343-355) ----------
  * pcs_pds_tv_step_slab = pcs_pds_tv_step on this rank's rows [row_begin, row_end) of its local H_loc x W arrays (halo
  * rows included), fused with the halo exchange: rows of x', z' that a row neighbour holds as halo are ALSO stored
- * into that neighbour's output arrays through NVLink, and the last block releases `epoch` into a flag word of each
- * neighbour.  Blocks that touch halo rows first acquire epoch-1 on the flag words the neighbours wrote.
- * peer_desc_host: HOST array of 18 int64
+ * into that neighbour's output arrays through NVLink.  Hand-over: every block that owns rows of the 16-row edge zone
+ * at the top / bottom of the slab adds (its zone rows) x (its output columns) to a uint32 counter word in the neighbour's
+ * memory when IT is done (system-scope release), so a side of step e is complete when that counter reads e * 16 * W
+ * (mod 2^32; epochs count from 1 and the words start at zero).  Blocks that touch halo rows first acquire the value of
+ * step epoch-1 on the counter words the neighbours add to.
+ * peer_desc_host: HOST array of 20 int64
  *   [0] x_up [1] z_up [2] x_dn [3] z_dn   device pointers to the neighbours' OUTPUT arrays (pcs_peer_open), 0 = none
  *   [4] plane_up [5] plane_dn             elements per z plane of the neighbour's arrays (its H_loc * W)
  *   [6] drow_up  [7] drow_dn              neighbour's local row index minus mine, for the same image row
  *   [8] nx_up [9] nx_dn [10] nz_up [11] nz_dn   my first / last updated rows of x (of z0, z1) that are pushed (<= 16)
- *   [12] wait_up [13] wait_dn             my uint32 flag words, written by the neighbours
- *   [14] sig_up  [15] sig_dn              uint32 flag words in the neighbours' memory
- *   [16] epoch (>= 1, +1 per step on every rank)   [17] device uint32 error word (set if a wait gave up after ~2 s)
+ *   [12] wait_up [13] wait_dn             my uint32 counter words, added to by the neighbours
+ *   [14] sig_up  [15] sig_dn              uint32 counter words in the neighbours' memory
+ *   [16] epoch (>= 1, +1 per step on every rank)   [17] device uint32 error word (set if a wait gave up)
+ *   [18] wait timeout in milliseconds (0 = 20 s)
+ *   [19] edge trim: rows by which the first / last row segment of every strip is shortened on the sides that have a
+ *        neighbour (rounded down to a multiple of 16, capped at 1/32 of the slab): the blocks that hand rows over to a
+ *        neighbour finish early and may start late, which hides the NVLink hand-over latency.  0 = equal segments.
  */
 PCS_DECL_REAL(pcs_pds_tv_step_slab,
               (void* x_out, void* z_out, const void* x, const void* z, const void* b, int64_t H_loc, int64_t W,

@@ -17,6 +17,62 @@ from typing import Any, Optional, Tuple
 from .map import Map
 
 
+class LazyDiagnostics:
+    """The diagnostics table of a solve, materialised as the reference's ``pandas.DataFrame`` on first use
+    (SURVEY.md 8(f)-4).  Building the frame costs ~0.2 ms of host time, during which the GPU would sit idle between two
+    back-to-back solves; everything a ``DataFrame`` offers (``diag['col']``, ``.loc``, ``.iloc``, ``len()``, ``print``,
+    ``.to_numpy()`` ...) is forwarded to the frame, ``diag.frame`` is the frame itself."""
+
+    __slots__ = ('_build', '_frame')
+
+    def __init__(self, build):
+        object.__setattr__(self, '_build', build)
+        object.__setattr__(self, '_frame', None)
+
+    @property
+    def frame(self):
+        if self._frame is None:
+            object.__setattr__(self, '_frame', self._build())
+            object.__setattr__(self, '_build', None)
+        return self._frame
+
+    def __getattr__(self, name):
+        return getattr(self.frame, name)
+
+    def __setattr__(self, name, value):
+        setattr(self.frame, name, value)
+
+    def __getitem__(self, key):
+        return self.frame[key]
+
+    def __setitem__(self, key, value):
+        self.frame[key] = value
+
+    def __len__(self):
+        return len(self.frame)
+
+    def __iter__(self):
+        return iter(self.frame)
+
+    def __contains__(self, key):
+        return key in self.frame
+
+    def __array__(self, dtype=None, copy=None):
+        import numpy as np
+        return np.asarray(self.frame, dtype=dtype)
+
+    def __eq__(self, other):
+        return self.frame == (other.frame if isinstance(other, LazyDiagnostics) else other)
+
+    __hash__ = None
+
+    def __repr__(self):
+        return repr(self.frame)
+
+    def _repr_html_(self):
+        return self.frame._repr_html_()
+
+
 class GenericIterativeAlgorithm(ABC):
     def __init__(self, objective_functional: Map, init_iterand: Any, max_iter: int = 500, min_iter: int = 10,
                  accuracy_threshold: float = 1e-3, verbose: Optional[int] = None):

@@ -32,7 +32,7 @@ from .._array import device, like_input, to_device, torch_dtype
 from ..core.functional import ProximableFunctional
 from ..core.linop import LinearOperator
 from ..core.map import DifferentiableMap
-from ..core.solver import GenericIterativeAlgorithm
+from ..core.solver import GenericIterativeAlgorithm, LazyDiagnostics
 from ..func.base import NullDifferentiableFunctional, NullProximableFunctional
 from ..linop.base import IdentityOperator, NullOperator
 
@@ -368,11 +368,19 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
             self._diag_reduced.add(it)
         super()._post_metric_copy(it)
 
+    def _metric_ready(self, it):
+        super()._metric_ready(it)
+        if self._slab is not None and self._plan is not None:
+            self._plan.check()               # a neighbour that stopped answering is reported now, not after max_iter updates
+
     def _reduce_diag(self, n):
         if self._slab is None:
             return
         idx = [i for i in range(n) if i not in self._diag_reduced]
-        if idx:
+        if idx and idx == list(range(idx[0], n)):         # the usual case: a contiguous tail of rows, one call in place
+            self._slab.all_reduce_sum(self._diag_dev[idx[0]:n])
+            self._diag_reduced.update(idx)
+        elif idx:
             sel = torch.tensor(idx, device=self._diag_dev.device)
             t = self._diag_dev.index_select(0, sel)
             self._slab.all_reduce_sum(t)
@@ -512,14 +520,18 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
         return row
 
     def _build_diagnostics(self, n):
-        from pandas import DataFrame
-        d = self._diag_host[:n].numpy()
-        with np.errstate(divide='ignore', invalid='ignore'):
-            rel = np.where(d[:, 1::2] == 0, np.inf, np.sqrt(d[:, 0::2]) / np.sqrt(d[:, 1::2]))
-        data = {'Iter': np.arange(n), 'Relative Improvement (primal variable)': rel[:, 0]}
-        if self._H:
-            data['Relative Improvement (dual variable)'] = rel[:, 1]
-        return DataFrame(data)
+        d = self._diag_host[:n].numpy().copy()           # the pinned rows are reused by the next solve
+        has_dual = self._H
+
+        def build():
+            from pandas import DataFrame
+            with np.errstate(divide='ignore', invalid='ignore'):
+                rel = np.where(d[:, 1::2] == 0, np.inf, np.sqrt(d[:, 0::2]) / np.sqrt(d[:, 1::2]))
+            data = {'Iter': np.arange(n), 'Relative Improvement (primal variable)': rel[:, 0]}
+            if has_dual:
+                data['Relative Improvement (dual variable)'] = rel[:, 1]
+            return DataFrame(data)
+        return LazyDiagnostics(build)
 
     def print_diagnostics(self):
         print(dict(self.diagnostics.loc[self.iter]))
@@ -697,11 +709,14 @@ class AcceleratedProximalGradientDescent(_DeviceLoop, GenericIterativeAlgorithm)
         return {'Iter': it, 'Relative Improvement': self._rel(float(d[0]), float(d[1]))}
 
     def _build_diagnostics(self, n):
-        from pandas import DataFrame
-        d = self._diag_host[:n].numpy()
-        with np.errstate(divide='ignore', invalid='ignore'):
-            rel = np.where(d[:, 1] == 0, np.inf, np.sqrt(d[:, 0]) / np.sqrt(d[:, 1]))
-        return DataFrame({'Iter': np.arange(n), 'Relative Improvement': rel})
+        d = self._diag_host[:n].numpy().copy()
+
+        def build():
+            from pandas import DataFrame
+            with np.errstate(divide='ignore', invalid='ignore'):
+                rel = np.where(d[:, 1] == 0, np.inf, np.sqrt(d[:, 0]) / np.sqrt(d[:, 1]))
+            return DataFrame({'Iter': np.arange(n), 'Relative Improvement': rel})
+        return LazyDiagnostics(build)
 
     def print_diagnostics(self):
         print(dict(self.diagnostics.loc[self.iter]))

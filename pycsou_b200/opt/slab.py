@@ -8,7 +8,9 @@ one update of the owned rows needs ``x`` on 14 rows above / 15 below and ``z`` o
 
 Per iteration NOTHING runs on the host but the one kernel launch: the fused kernel (``csrc/pcs_pds.cu``) stores the
 boundary rows of ``x', z'`` straight into the neighbours' halo rows through NVLink (peer mappings from
-``csrc/pcs_peer.cu``) and hands over with a release/acquire flag word per neighbour.  The four norms of the stop test
+``csrc/pcs_peer.cu``) and hands over through one counter word per neighbour: every block that owns rows of the 16-row
+edge zone adds its share with a system-scope release as soon as it is done, and the neighbour's edge blocks of the next
+step acquire the full count (``PCS_SLAB_TIMEOUT_S``, default 20 s, bounds the device-side wait).  The four norms of the stop test
 are summed over ranks with one 32-byte all-reduce, only on the iterations whose stop test is live.
 
 What runs once per solve (scattering ``y``'s halo rows to form ``A^T y``, filling the halos of ``x0, z0``) uses plain
@@ -28,9 +30,10 @@ Operators and functionals describe the GLOBAL problem; data, ``x0``/``z0`` and t
 from __future__ import annotations
 
 import ctypes as C
+import os
+import weakref
 
 import numpy as np
-import weakref
 
 import torch
 import torch.distributed as dist
@@ -346,29 +349,69 @@ class SlabPdsTvPlan:
         nbytes = int(_lib.call_plain('pcs_pds_tv_workspace_bytes'))
         self.ws = torch.zeros(nbytes // 8, dtype=torch.float64, device=dev)
         self.err = torch.zeros(4, dtype=torch.int32, device=dev)
-        self._desc = np.zeros(18, dtype=np.int64)
+        self._desc = np.zeros(20, dtype=np.int64)
         self._K = K
         self._static_desc()
         comm.barrier()
 
+    def _exchange_rows(self, buf, above, below):
+        """Fill the first ``above`` / last ``below`` rows of ``buf`` ((above + n_own + below) x W, own rows already in the
+        middle) with the neighbours' rows; rows beyond the image edge are left untouched (callers keep them zero)."""
+        comm, lay = self.comm, self.lay
+        rank, world, n = comm.rank, comm.world, lay.n_own
+        g = (lambda r: r) if comm.group is None else (lambda r: dist.get_global_rank(comm.group, r))
+        if _stage_on_host(buf, comm.group):               # gloo control plane (single-GPU tests): through the host
+            ext = gather_halo(buf[above:above + n].cpu(), above, below, rank, world, comm.group)
+            lo = above if rank == 0 else 0
+            buf[lo:lo + ext.shape[0]].copy_(ext)
+            return
+        ops = []
+        if rank > 0:
+            if below:
+                ops.append(dist.P2POp(dist.isend, buf[above:above + below], g(rank - 1), comm.group))
+            if above:
+                ops.append(dist.P2POp(dist.irecv, buf[:above], g(rank - 1), comm.group))
+        if rank < world - 1:
+            if above:
+                ops.append(dist.P2POp(dist.isend, buf[n:n + above], g(rank + 1), comm.group))
+            if below:
+                ops.append(dist.P2POp(dist.irecv, buf[above + n:], g(rank + 1), comm.group))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+
     def begin_solve(self):
         """Per-solve precomputation (collective: one halo exchange of ``y``): the data term on the local rows
-        ``[row_begin, row_end]`` -- ``y`` itself, or ``A^T y`` for the deconvolution problems."""
+        ``[row_begin, row_end]`` -- ``y`` itself, or ``A^T y`` for the deconvolution problems.  The extended copy of
+        ``y`` and the local convolution operator are set up once per plan; every solve re-reads ``y`` (it may have been
+        modified in place), exchanges its boundary rows and re-forms ``A^T y``."""
         from . import _fused as Fz
         if self.data_mode == Fz.DM_NONE:
             return
         lay, comm, W = self.lay, self.comm, self.lay.W
         bv = self.b.view(lay.H_loc, W)
+        above, below = (0, 1) if self.data_mode == Fz.DM_IDENTITY else (Y_UP, Y_DN)
+        if getattr(self, '_ext', None) is None:
+            self._ext = torch.zeros(above + lay.n_own + below, W, dtype=self.dtype, device=self.b.device)
+            if self.data_mode == Fz.DM_CONV:
+                # rows beyond the image edge stay zero = the zero boundary of the convolution; the first / last rank
+                # simply drop them from the local operator's array
+                from ..linop.conv import Convolve2D
+                self._ext_lo = above if comm.rank == 0 else 0
+                self._ext_hi = above + lay.n_own + (0 if comm.rank == comm.world - 1 else below)
+                rows = self._ext_hi - self._ext_lo
+                self._A_loc = Convolve2D(size=rows * W, filter=self._A.filter, shape=(rows, W))
+        ext = self._ext
+        ext[above:above + lay.n_own].copy_(self._y_own)
+        self._exchange_rows(ext, above, below)
         if self.data_mode == Fz.DM_IDENTITY:
-            ext = gather_halo(self._y_own, 0, 1, comm.rank, comm.world, comm.group)
-            bv[lay.row_begin:lay.row_begin + ext.shape[0]] = ext
+            keep = lay.n_own + (1 if comm.rank < comm.world - 1 else 0)
+            bv[lay.row_begin:lay.row_begin + keep] = ext[:keep]
         else:
             # A^T y on the rows [r0, r1]: y with Y_UP rows above / Y_DN below, filtered with the zero boundary (the
             # true one at the image edge), keeping the rows at least Y_UP away from a cut
-            from ..linop.conv import Convolve2D
-            ext = gather_halo(self._y_own, Y_UP, Y_DN, comm.rank, comm.world, comm.group).contiguous()
-            A_loc = Convolve2D(size=ext.numel(), filter=self._A.filter, shape=tuple(ext.shape))
-            bt = A_loc._adjoint(ext.reshape(-1)).view(ext.shape)
+            loc = ext[self._ext_lo:self._ext_hi]
+            bt = self._A_loc._adjoint(loc.reshape(-1)).view(loc.shape)
             skip = Y_UP if comm.rank > 0 else 0
             keep = lay.n_own + (1 if comm.rank < comm.world - 1 else 0)
             bv[lay.row_begin:lay.row_begin + keep] = bt[skip:skip + keep]
@@ -388,6 +431,8 @@ class SlabPdsTvPlan:
                 # the neighbour waits on the word reserved for ITS neighbour on my side: I am "below" the rank above
                 d[isg] = self.arena.remote[side] + m[r]['off_flags'] + (4 if side < 0 else 0)
         d[17] = self.err.data_ptr()
+        d[18] = int(float(os.environ.get('PCS_SLAB_TIMEOUT_S', '20')) * 1000)     # device-side wait timeout
+        d[19] = int(os.environ.get('PCS_SLAB_TRIM', '0'))      # shorter edge segments (rows); measured: no gain, off
 
     def _peer_desc(self, out_index: int):
         d, m = self._desc, self.arena.meta
