@@ -291,6 +291,23 @@ PCS_DECL_REAL(pcs_pds_tv_step_slab,
                double step0, double step1, int strip_cols, int nseg, int use_tma, void* diag_out_f64, void* workspace,
                void* stream, const int64_t* peer_desc_host))
 
+/* ---- Condat-Vu total-variation iteration for ANY 2-D Gradient kind (forward / centered / backward, edge rows as in
+ *      pylops; pycsou/linop/diff.py:777-882 -- `centered` is pycsou's default) in two kernels per update
+ *      (pycsou/opt/proxalgs.py:343-394).  kind: 0 forward, 1 centered, 2 backward.  Arrays are H x W (z: two planes).
+ *   primal: a = K^T z; xt = prox_{tau G}(x - tau g - tau a); u_out = 2 xt - x; x_out = rho xt + (1 - rho) x;
+ *           diag_out_f64[0..1] = ||x_out - x||^2, ||x||^2.   data_mode 0: g = 0; 1: g = x - b (b = y); 3: g = b (given).
+ *           g_mode 0 none, 1 NonNegativeOrthant, 2 Segment[g_a, g_b], 3 L1 with threshold g_a (= tau * lam_G).
+ *   dual:   zt = fenchel_prox_{sigma H}(z + sigma K u); z_out = rho zt + (1 - rho) z;
+ *           diag_out_f64[2..3] = ||z_out - z||^2, ||z||^2.   h_mode 0: lam * L21 (isotropic TV), 1: lam * L1.
+ *   workspace: pcs_pds_tv_workspace_bytes() bytes, zero-initialised once (shared with pcs_pds_tv_step). */
+PCS_DECL_REAL(pcs_pds_grad_primal_step,
+              (void* x_out, void* u_out, const void* x, const void* b, const void* z, int64_t H, int64_t W, int kind,
+               int edge, int data_mode, int g_mode, double g_a, double g_b, double tau, double rho, double step0,
+               double step1, void* diag_out_f64, void* workspace, void* stream))
+PCS_DECL_REAL(pcs_pds_grad_dual_step,
+              (void* z_out, const void* u, const void* z, int64_t H, int64_t W, int kind, int edge, int h_mode, double lam,
+               double sigma, double rho, double step0, double step1, void* diag_out_f64, void* workspace, void* stream))
+
 /* Peer memory (CUDA IPC): the only entry points that own device memory.  A rank allocates its slab arena, publishes
  * the pcs_peer_handle_bytes()-byte handle, and maps its row neighbours' arenas. */
 int pcs_peer_handle_bytes(void);

@@ -70,6 +70,9 @@ REAL = {
                        [I32] * 3 + [P, P, P],
     'pcs_pds_tv_run': [P] * 5 + [I64, I64] + [I32, I32, P, P, P] + [I32] * 4 + [I32, F64, F64, I32] + [F64] * 6 +
                       [I32] * 3 + [I64, P, P, P],
+    # two-kernel Condat-Vu TV update for any 2-D Gradient kind (csrc/pcs_pds_grad.cu)
+    'pcs_pds_grad_primal_step': [P] * 5 + [I64, I64, I32, I32, I32, I32] + [F64] * 6 + [P, P, P],
+    'pcs_pds_grad_dual_step': [P] * 3 + [I64, I64, I32, I32, I32] + [F64] * 5 + [P, P, P],
     # a whole APGD solve (flat Convolve1D data term) in one launch (csrc/pcs_apgd.cu)
     'pcs_apgd_conv1d_run': [P, P, P, P, I32, I32, I64, I32, F64, F64, I32, F64, F64, I64, I64, I64, F64, P, P, P],
     # ... fused with the halo push / flag handshake of the slab decomposition (last argument: HOST int64[18])

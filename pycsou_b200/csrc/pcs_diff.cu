@@ -5,7 +5,8 @@
 // oracle/pylops_standin.py.  Any n-D C-order array differentiated along one axis is viewed as
 // (outer, n, inner); consecutive threads walk consecutive flat indices, so every access is coalesced and the
 // +-inner neighbours are served by L1/L2 (HBM sees each element once).
-#include "pcs_diff.cuh"
+#include "pcs_tile2d.cuh"
+#include <algorithm>
 
 using namespace pcs;
 
@@ -77,24 +78,82 @@ PCS_EXPORT_REAL(pcs_secondderiv_adj, DERIV_PARAMS, DERIV_ARGS)
 
 // ------------------------------------------------------------------------------------------------ 2-D gradient
 // out = [d/daxis0 ; d/daxis1] (two planes of H*W), pylops Gradient = VStack of per-axis FirstDerivative.
-template <typename T>
-__global__ void __launch_bounds__(DF_BLOCK) grad2d_fwd_kernel(T* __restrict__ out, const T* __restrict__ x, int64_t H,
-                                                              int64_t W, int kind, int edge, T ih0, T ih1) {
-    const int64_t N = H * W, stride = (int64_t)gridDim.x * DF_BLOCK;
-    for (int64_t f = (int64_t)blockIdx.x * DF_BLOCK + threadIdx.x; f < N; f += stride) {
-        const int64_t r = f / W, c = f - r * W;
-        out[f] = d1_fwd<T>(x + f, r, H, W, kind, edge, ih0);
-        out[N + f] = d1_fwd<T>(x + f, c, W, 1, kind, edge, ih1);
+// (two rows of loads in flight per thread: measured 4.7-5.0 TB/s at 4096^2 against 4.2-4.4 with one, profiles/r02_tile_sweep.txt;
+// the Condat-Vu pair of pcs_pds_grad.cu, which carries more registers per row, is fastest with one)
+constexpr int GRAD_GROUP = 2;
+// Row-tiled kernels (pcs_tile2d.cuh): 128-bit coalesced accesses, three-row register window, lane shuffles for the
+// column neighbours, no per-element index arithmetic.  Algorithmic traffic: forward 3 N s, adjoint 3 N s.
+template <typename T, int V, int KIND>
+__global__ void __launch_bounds__(T2_BLOCK) grad2d_fwd_kernel(T* __restrict__ out, const T* __restrict__ x, int H, int W,
+                                                              int edge, T ih0, T ih1) {
+    const Tiles tl = tiles_of<V>(H, W);
+    const int lane = threadIdx.x & 31;
+    T* __restrict__ out1 = out + (int64_t)H * W;
+    for (long long t = blockIdx.x; t < tl.n; t += gridDim.x) {
+        const int ty = (int)(t / tl.ntx), tx = (int)(t - (long long)ty * tl.ntx);
+        const int j0 = (tx * T2_BLOCK + (int)threadIdx.x) * V;
+        const int r0 = ty * T2_ROWS, r1 = min(H, r0 + T2_ROWS);
+        const ColCoef<T, V> kc = col_coef<T, V, KIND, false>(edge, j0, W, ih1);
+        Pack<T, V> m = row_load<T, V>(x, r0 - 1, H, W, j0);
+        Pack<T, V> c = row_load<T, V>(x, r0, H, W, j0);
+        for (int i0 = r0; i0 < r1; i0 += GRAD_GROUP) {
+            Pack<T, V> nx[GRAD_GROUP];
+#pragma unroll
+            for (int g = 0; g < GRAD_GROUP; ++g) nx[g] = row_load<T, V>(x, i0 + g + 1, H, W, j0);
+#pragma unroll
+            for (int g = 0; g < GRAD_GROUP; ++g) {
+                const int i = i0 + g;
+                if (i < r1) {                                   // (uniform over the block: the shuffles below are safe)
+                    const T* __restrict__ row = x + (int64_t)i * W;
+                    pack_store<T, V>(out + (int64_t)i * W, j0, W,
+                                     row_stencil<T, V>(m, c, nx[g], d1_row<T, KIND>(edge, i, H, ih0)));
+                    T l, r;
+                    row_neighbours<T, V>(row, c, j0, W, lane, l, r);
+                    pack_store<T, V>(out1 + (int64_t)i * W, j0, W, col_stencil<T, V>(c, l, r, kc));
+                }
+                m = c;
+                c = nx[g];
+            }
+        }
     }
 }
 
-template <typename T>
-__global__ void __launch_bounds__(DF_BLOCK) grad2d_adj_kernel(T* __restrict__ out, const T* __restrict__ z, int64_t H,
-                                                              int64_t W, int kind, int edge, T ih0, T ih1) {
-    const int64_t N = H * W, stride = (int64_t)gridDim.x * DF_BLOCK;
-    for (int64_t f = (int64_t)blockIdx.x * DF_BLOCK + threadIdx.x; f < N; f += stride) {
-        const int64_t r = f / W, c = f - r * W;
-        out[f] = d1_adj<T>(z + f, r, H, W, kind, edge, ih0) + d1_adj<T>(z + N + f, c, W, 1, kind, edge, ih1);
+template <typename T, int V, int KIND>
+__global__ void __launch_bounds__(T2_BLOCK) grad2d_adj_kernel(T* __restrict__ out, const T* __restrict__ z, int H, int W,
+                                                              int edge, T ih0, T ih1) {
+    const Tiles tl = tiles_of<V>(H, W);
+    const int lane = threadIdx.x & 31;
+    const T* __restrict__ z1 = z + (int64_t)H * W;
+    for (long long t = blockIdx.x; t < tl.n; t += gridDim.x) {
+        const int ty = (int)(t / tl.ntx), tx = (int)(t - (long long)ty * tl.ntx);
+        const int j0 = (tx * T2_BLOCK + (int)threadIdx.x) * V;
+        const int r0 = ty * T2_ROWS, r1 = min(H, r0 + T2_ROWS);
+        const ColCoef<T, V> kc = col_coef<T, V, KIND, true>(edge, j0, W, ih1);
+        Pack<T, V> m = row_load<T, V>(z, r0 - 1, H, W, j0);
+        Pack<T, V> c = row_load<T, V>(z, r0, H, W, j0);
+        for (int i0 = r0; i0 < r1; i0 += GRAD_GROUP) {
+            Pack<T, V> nx[GRAD_GROUP], c1[GRAD_GROUP];
+#pragma unroll
+            for (int g = 0; g < GRAD_GROUP; ++g) {
+                nx[g] = row_load<T, V>(z, i0 + g + 1, H, W, j0);
+                c1[g] = row_load<T, V>(z1, i0 + g, H, W, j0);
+            }
+#pragma unroll
+            for (int g = 0; g < GRAD_GROUP; ++g) {
+                const int i = i0 + g;
+                if (i < r1) {
+                    Pack<T, V> o = row_stencil<T, V>(m, c, nx[g], d1_row_adj<T, KIND>(edge, i, H, ih0));
+                    T l, r;
+                    row_neighbours<T, V>(z1 + (int64_t)i * W, c1[g], j0, W, lane, l, r);
+                    const Pack<T, V> a1 = col_stencil<T, V>(c1[g], l, r, kc);
+#pragma unroll
+                    for (int e = 0; e < V; ++e) o.v[e] += a1.v[e];
+                    pack_store<T, V>(out + (int64_t)i * W, j0, W, o);
+                }
+                m = c;
+                c = nx[g];
+            }
+        }
     }
 }
 
@@ -115,8 +174,18 @@ static int pcs_grad2d_fwd_impl(T* out, const T* x, int64_t H, int64_t W, int kin
                                cudaStream_t s) {
     int rc = grad2d_check<T>(out, x, H, W, kind, edge, s0, s1, "pcs_grad2d_fwd");
     if (rc || H * W == 0) return rc;
-    grad2d_fwd_kernel<T><<<grid_for(H * W, DF_BLOCK, DF_CTAS_PER_SM), DF_BLOCK, 0, s>>>(out, x, H, W, kind, edge,
-                                                                                      (T)(1.0 / s0), (T)(1.0 / s1));
+    PCS_REQUIRE(H < (1ll << 31) - 64 && W < (1ll << 31) - 4096, "pcs_grad2d_fwd: image side too large");
+    constexpr int VEC = 16 / (int)sizeof(T);
+    const T ih0 = (T)(1.0 / s0), ih1 = (T)(1.0 / s1);
+    if (t2_vec_ok<T>(W, {out, x})) {
+        const Tiles tl = tiles_of<VEC>((int)H, (int)W);
+        const int grid = (int)std::min<long long>(tl.n, (long long)num_sms() * T2_GRID_PER_SM);
+        PCS_KIND_SWITCH(kind, (grad2d_fwd_kernel<T, VEC, KIND><<<grid, T2_BLOCK, 0, s>>>(out, x, (int)H, (int)W, edge, ih0, ih1)));
+    } else {
+        const Tiles tl = tiles_of<1>((int)H, (int)W);
+        const int grid = (int)std::min<long long>(tl.n, (long long)num_sms() * T2_GRID_PER_SM);
+        PCS_KIND_SWITCH(kind, (grad2d_fwd_kernel<T, 1, KIND><<<grid, T2_BLOCK, 0, s>>>(out, x, (int)H, (int)W, edge, ih0, ih1)));
+    }
     return check_launch("pcs_grad2d_fwd");
 }
 PCS_EXPORT_REAL(pcs_grad2d_fwd,
@@ -129,8 +198,18 @@ static int pcs_grad2d_adj_impl(T* out, const T* z, int64_t H, int64_t W, int kin
                                cudaStream_t s) {
     int rc = grad2d_check<T>(out, z, H, W, kind, edge, s0, s1, "pcs_grad2d_adj");
     if (rc || H * W == 0) return rc;
-    grad2d_adj_kernel<T><<<grid_for(H * W, DF_BLOCK, DF_CTAS_PER_SM), DF_BLOCK, 0, s>>>(out, z, H, W, kind, edge,
-                                                                                      (T)(1.0 / s0), (T)(1.0 / s1));
+    PCS_REQUIRE(H < (1ll << 31) - 64 && W < (1ll << 31) - 4096, "pcs_grad2d_adj: image side too large");
+    constexpr int VEC = 16 / (int)sizeof(T);
+    const T ih0 = (T)(1.0 / s0), ih1 = (T)(1.0 / s1);
+    if (t2_vec_ok<T>(W, {out, z})) {
+        const Tiles tl = tiles_of<VEC>((int)H, (int)W);
+        const int grid = (int)std::min<long long>(tl.n, (long long)num_sms() * T2_GRID_PER_SM);
+        PCS_KIND_SWITCH(kind, (grad2d_adj_kernel<T, VEC, KIND><<<grid, T2_BLOCK, 0, s>>>(out, z, (int)H, (int)W, edge, ih0, ih1)));
+    } else {
+        const Tiles tl = tiles_of<1>((int)H, (int)W);
+        const int grid = (int)std::min<long long>(tl.n, (long long)num_sms() * T2_GRID_PER_SM);
+        PCS_KIND_SWITCH(kind, (grad2d_adj_kernel<T, 1, KIND><<<grid, T2_BLOCK, 0, s>>>(out, z, (int)H, (int)W, edge, ih0, ih1)));
+    }
     return check_launch("pcs_grad2d_adj");
 }
 PCS_EXPORT_REAL(pcs_grad2d_adj,

@@ -65,9 +65,9 @@ class _NoMatch(Exception):
     pass
 
 
-def _match_K(Kop, dim):
+def _match_K(Kop, dim, any_kind=False):
     from ..linop.diff import GradientOperator
-    if not isinstance(Kop, GradientOperator) or Kop.kind != 'forward' or len(Kop.array_shape) != 2:
+    if not isinstance(Kop, GradientOperator) or len(Kop.array_shape) != 2 or (Kop.kind != 'forward' and not any_kind):
         raise _NoMatch('K is not a 2-D forward-difference Gradient')
     H, W = Kop.array_shape
     if H * W != dim or H < 2 or W < 2:
@@ -256,6 +256,46 @@ def last_launch():
     return d
 
 
+class PdsGradPlan:
+    """Two-launch-per-iteration Condat-Vu TV solver for ANY 2-D ``Gradient`` kind (``csrc/pcs_pds_grad.cu``): pycsou's
+    default ``kind='centered'`` and ``'backward'`` reach one row / column behind as well as ahead, which the one-kernel
+    update (forward differences) does not cover.  ``F`` in {None, 1/2 SquaredL2Loss, anything differentiable (its
+    gradient is evaluated by the stand-alone kernels and handed to the primal kernel)}."""
+
+    def __init__(self, solver, H, W, steps, kind, edge, data_mode, y, g, h):
+        self.solver = weakref.proxy(solver)
+        self.H, self.W, self.steps = H, W, steps
+        self.kind, self.edge = K.KIND[kind], int(bool(edge))
+        self.data_mode = data_mode
+        self.g_mode, self.g_a, self.g_b = g
+        self.h_mode, self.lam = h
+        self.dtype = dt = solver._dtype
+        self.sfx = '_f32' if dt == torch.float32 else '_f64'
+        self.b = to_device(y, dt) if data_mode == DM_IDENTITY else None
+        if self.b is not None and self.b.numel() != H * W:
+            raise _NoMatch('data size mismatch')
+        nbytes = int(_lib.call_plain('pcs_pds_tv_workspace_bytes'))
+        self.ws = torch.zeros(nbytes // 8, dtype=torch.float64, device=K_device())
+        self.u = torch.empty(H * W, dtype=dt, device=K_device())
+        self._xbuf, self._zbuf = [None, None], [None, None]
+
+    _out = PdsTvPlan._out
+    release = PdsTvPlan.release
+
+    def step(self, x, z, drow):
+        s = self.solver
+        b = s.F._gradient(x) if self.data_mode == DM_GIVEN else self.b
+        xo, zo = self._out(self._xbuf, x), self._out(self._zbuf, z)
+        st = K.stream()
+        _lib.call('pcs_pds_grad_primal_step' + self.sfx, xo.data_ptr(), self.u.data_ptr(), x.data_ptr(), K.ptr(b),
+                  z.data_ptr(), self.H, self.W, self.kind, self.edge, self.data_mode, self.g_mode, self.g_a, self.g_b,
+                  float(s.tau), float(s.rho), self.steps[0], self.steps[1], drow.data_ptr(), self.ws.data_ptr(), st)
+        _lib.call('pcs_pds_grad_dual_step' + self.sfx, zo.data_ptr(), self.u.data_ptr(), z.data_ptr(), self.H, self.W,
+                  self.kind, self.edge, self.h_mode, self.lam, float(s.sigma), float(s.rho), self.steps[0], self.steps[1],
+                  drow.data_ptr(), self.ws.data_ptr(), st)
+        return xo, zo
+
+
 def _run_many(self, x, z, n, drows):
     """``n`` consecutive updates enqueued by ONE library call (``pcs_pds_tv_run``); ``drows``: n x 4 diagnostics rows."""
     s = self.solver
@@ -393,13 +433,20 @@ def plan_pds(solver):
     if not solver._H or solver._dtype not in (torch.float32, torch.float64):
         return None
     try:
-        H, W, steps = _match_K(solver.K, solver.dim)
+        H, W, steps = _match_K(solver.K, solver.dim, any_kind=True)
         h = _match_H(solver.H, H * W)
         g = _match_G(solver.G, float(solver.tau))
         data_mode, y, A = _match_F(solver.F, (H, W))
         if not (float(solver.tau) > 0 and float(solver.sigma) > 0):
             raise _NoMatch('non-positive step')
-        return PdsTvPlan(solver, H, W, steps, data_mode, y, A, g, h)
+        if solver.K.kind == 'forward':
+            return PdsTvPlan(solver, H, W, steps, data_mode, y, A, g, h)
+        # centred / backward differences: two kernels per update; a convolution data term is evaluated op by op
+        if data_mode == DM_CONV:
+            data_mode, y = DM_GIVEN, None
+        if h[1] <= 0:
+            raise _NoMatch('non-positive regularisation weight')
+        return PdsGradPlan(solver, H, W, steps, solver.K.kind, solver.K.edge, data_mode, y, g, h)
     except _NoMatch:
         return None
 

@@ -111,6 +111,8 @@ def test_c2_variants(name, fused):
         est, _, _ = s.iterate()
         assert rel_l2(est['primal_variable'], g[f'x_k{k}']) < TOL64
         assert rel_l2(est['dual_variable'], g[f'z_k{k}']) < TOL64
+        want = None if not fused else ('PdsGradPlan' if name.endswith('centered_pds') else 'PdsTvPlan')
+        assert (type(s._plan).__name__ if s._plan is not None else None) == want     # centred differences are fused too
 
 
 def _deconv_solver(m, shape, psf, y, lam, k, dtype, fused):
