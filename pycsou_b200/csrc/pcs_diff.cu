@@ -28,6 +28,111 @@ __global__ void __launch_bounds__(DF_BLOCK) deriv_kernel(T* __restrict__ out, co
     }
 }
 
+// ---- first derivative along one axis, row-tiled (pcs_tile2d.cuh) ------------------------------------------------------
+// (outer, n, inner) with inner > 1: `outer` images of n rows x inner columns, stencil down the rows (three-row register
+// window); inner == 1: outer rows of n samples, stencil along the row (lane shuffles).  128-bit accesses where the rows are
+// 16-byte multiples.  ADJ: gather form of the transpose.  accumulate: out += (n-D Gradient adjoint sums its axes).
+constexpr int DERIV_GROUP = 2;
+template <typename T, int V, int KIND, bool ADJ>
+__global__ void __launch_bounds__(T2_BLOCK) deriv_rows_kernel(T* __restrict__ out, const T* __restrict__ x, int64_t outer,
+                                                              int n, int inner, int edge, T ih, int accumulate) {
+    const Tiles tl = tiles_of<V>(n, inner);
+    const long long total = (long long)outer * tl.n;
+    for (long long t = blockIdx.x; t < total; t += gridDim.x) {
+        const long long img = t / tl.n, tt = t - img * tl.n;
+        const int ty = (int)(tt / tl.ntx), tx = (int)(tt - (long long)ty * tl.ntx);
+        const int j0 = (tx * T2_BLOCK + (int)threadIdx.x) * V;
+        const int r0 = ty * T2_ROWS, r1 = min(n, r0 + T2_ROWS);
+        const T* __restrict__ xi = x + img * (int64_t)n * inner;
+        T* __restrict__ oi = out + img * (int64_t)n * inner;
+        Pack<T, V> m = row_load<T, V>(xi, r0 - 1, n, inner, j0);
+        Pack<T, V> c = row_load<T, V>(xi, r0, n, inner, j0);
+        for (int i0 = r0; i0 < r1; i0 += DERIV_GROUP) {
+            Pack<T, V> nx[DERIV_GROUP], acc[DERIV_GROUP];
+#pragma unroll
+            for (int g = 0; g < DERIV_GROUP; ++g) {
+                nx[g] = row_load<T, V>(xi, i0 + g + 1, n, inner, j0);
+                acc[g] = (accumulate && i0 + g < r1) ? row_load<T, V>(oi, i0 + g, n, inner, j0) : pack_zero<T, V>();
+            }
+#pragma unroll
+            for (int g = 0; g < DERIV_GROUP; ++g) {
+                const int i = i0 + g;
+                if (i < r1) {
+                    const Coef3<T> k = ADJ ? d1_row_adj<T, KIND>(edge, i, n, ih) : d1_row<T, KIND>(edge, i, n, ih);
+                    Pack<T, V> o = row_stencil<T, V>(m, c, nx[g], k);
+#pragma unroll
+                    for (int e = 0; e < V; ++e) o.v[e] += acc[g].v[e];
+                    pack_store<T, V>(oi + (int64_t)i * inner, j0, inner, o);
+                }
+                m = c;
+                c = nx[g];
+            }
+        }
+    }
+}
+
+template <typename T, int V, int KIND, bool ADJ>
+__global__ void __launch_bounds__(T2_BLOCK) deriv_cols_kernel(T* __restrict__ out, const T* __restrict__ x, int rows, int n,
+                                                              int edge, T ih, int accumulate) {
+    const Tiles tl = tiles_of<V>(rows, n);
+    const int lane = threadIdx.x & 31;
+    for (long long t = blockIdx.x; t < tl.n; t += gridDim.x) {
+        const int ty = (int)(t / tl.ntx), tx = (int)(t - (long long)ty * tl.ntx);
+        const int j0 = (tx * T2_BLOCK + (int)threadIdx.x) * V;
+        const int r0 = ty * T2_ROWS, r1 = min(rows, r0 + T2_ROWS);
+        const ColCoef<T, V> kc = col_coef<T, V, KIND, ADJ>(edge, j0, n, ih);
+        for (int i0 = r0; i0 < r1; i0 += DERIV_GROUP) {
+            Pack<T, V> c[DERIV_GROUP], acc[DERIV_GROUP];
+#pragma unroll
+            for (int g = 0; g < DERIV_GROUP; ++g) {
+                c[g] = row_load<T, V>(x, i0 + g, rows, n, j0);
+                acc[g] = (accumulate && i0 + g < r1) ? row_load<T, V>(out, i0 + g, rows, n, j0) : pack_zero<T, V>();
+            }
+#pragma unroll
+            for (int g = 0; g < DERIV_GROUP; ++g) {
+                const int i = i0 + g;
+                if (i < r1) {                                   // (uniform over the block: the shuffles are safe)
+                    T l, r;
+                    row_neighbours<T, V>(x + (int64_t)i * n, c[g], j0, n, lane, l, r);
+                    Pack<T, V> o = col_stencil<T, V>(c[g], l, r, kc);
+#pragma unroll
+                    for (int e = 0; e < V; ++e) o.v[e] += acc[g].v[e];
+                    pack_store<T, V>(out + (int64_t)i * n, j0, n, o);
+                }
+            }
+        }
+    }
+}
+
+template <typename T, bool ADJ>
+static bool deriv_tiled(T* out, const T* x, int64_t outer, int64_t n, int64_t inner, int kind, int edge, T ih,
+                        int accumulate, cudaStream_t s) {
+    constexpr int VEC = 16 / (int)sizeof(T);
+    const int64_t lim = (1ll << 31) - 4096;
+    if (n >= lim || inner >= lim) return false;
+    if (inner > 1) {
+        const bool vec = t2_vec_ok<T>(inner, {out, x});
+        const Tiles tl = vec ? tiles_of<VEC>((int)n, (int)inner) : tiles_of<1>((int)n, (int)inner);
+        const int grid = (int)std::min<long long>(std::max<long long>(outer * tl.n, 1), (long long)num_sms() * T2_GRID_PER_SM);
+        if (vec) {
+            PCS_KIND_SWITCH(kind, (deriv_rows_kernel<T, VEC, KIND, ADJ><<<grid, T2_BLOCK, 0, s>>>(out, x, outer, (int)n, (int)inner, edge, ih, accumulate)));
+        } else {
+            PCS_KIND_SWITCH(kind, (deriv_rows_kernel<T, 1, KIND, ADJ><<<grid, T2_BLOCK, 0, s>>>(out, x, outer, (int)n, (int)inner, edge, ih, accumulate)));
+        }
+        return true;
+    }
+    if (outer >= lim) return false;
+    const bool vec = t2_vec_ok<T>(n, {out, x});
+    const Tiles tl = vec ? tiles_of<VEC>((int)outer, (int)n) : tiles_of<1>((int)outer, (int)n);
+    const int grid = (int)std::min<long long>(std::max<long long>(tl.n, 1), (long long)num_sms() * T2_GRID_PER_SM);
+    if (vec) {
+        PCS_KIND_SWITCH(kind, (deriv_cols_kernel<T, VEC, KIND, ADJ><<<grid, T2_BLOCK, 0, s>>>(out, x, (int)outer, (int)n, edge, ih, accumulate)));
+    } else {
+        PCS_KIND_SWITCH(kind, (deriv_cols_kernel<T, 1, KIND, ADJ><<<grid, T2_BLOCK, 0, s>>>(out, x, (int)outer, (int)n, edge, ih, accumulate)));
+    }
+    return true;
+}
+
 template <typename T, bool ADJ, bool SECOND>
 static int deriv_launch(T* out, const T* x, int64_t outer, int64_t n, int64_t inner, int kind, int edge, double step,
                         int accumulate, cudaStream_t s, const char* what) {
@@ -41,6 +146,9 @@ static int deriv_launch(T* out, const T* x, int64_t outer, int64_t n, int64_t in
     PCS_REQUIRE(!SECOND || !edge || n >= 3, "%s: edge=True needs at least 3 samples along the axis", what);
     PCS_REQUIRE(SECOND || kind != 1 || !edge || n >= 2, "%s: edge=True needs at least 2 samples along the axis", what);
     const T inv_h = SECOND ? (T)(1.0 / (step * step)) : (T)(1.0 / step);
+    if constexpr (!SECOND) {
+        if (deriv_tiled<T, ADJ>(out, x, outer, n, inner, kind, edge, inv_h, accumulate, s)) return check_launch(what);
+    }
     deriv_kernel<T, ADJ, SECOND><<<grid_for(total, DF_BLOCK, DF_CTAS_PER_SM), DF_BLOCK, 0, s>>>(
         out, x, outer, n, inner, kind, edge, inv_h, accumulate);
     return check_launch(what);
@@ -232,6 +340,84 @@ __global__ void __launch_bounds__(DF_BLOCK) lap2d_kernel(T* __restrict__ out, co
     }
 }
 
+// Row-tiled Laplacian: the interior stencil (1, -2, 1) per axis runs on the tiles (rows / columns 0 and n-1 produce
+// zero, i.e. pylops' edge=False rule; the transpose gathers with the transposed entries); with edge=True the three
+// outermost rows / columns differ (one-sided second differences reach two samples inwards) and a frame kernel
+// recomputes those few pixels with the scalar formulas of pcs_diff.cuh.
+template <typename T> __device__ __forceinline__ Coef3<T> d2_row(int i, int n) {
+    Coef3<T> r = {T(0), T(0), T(0)};
+    if (i >= 1 && i <= n - 2) { r.m = T(1); r.c = T(-2); r.p = T(1); }
+    return r;
+}
+template <typename T, bool ADJ> __device__ __forceinline__ Coef3<T> d2_coef(int i, int n) {
+    if (!ADJ) return d2_row<T>(i, n);
+    Coef3<T> r;
+    r.m = d2_row<T>(i - 1, n).p;
+    r.c = d2_row<T>(i, n).c;
+    r.p = d2_row<T>(i + 1, n).m;
+    return r;
+}
+template <typename T, int V, bool ADJ>
+__global__ void __launch_bounds__(T2_BLOCK) lap2d_tiled_kernel(T* __restrict__ out, const T* __restrict__ x, int H, int W,
+                                                               T w0ih, T w1ih) {
+    const Tiles tl = tiles_of<V>(H, W);
+    const int lane = threadIdx.x & 31;
+    for (long long t = blockIdx.x; t < tl.n; t += gridDim.x) {
+        const int ty = (int)(t / tl.ntx), tx = (int)(t - (long long)ty * tl.ntx);
+        const int j0 = (tx * T2_BLOCK + (int)threadIdx.x) * V;
+        const int r0 = ty * T2_ROWS, r1 = min(H, r0 + T2_ROWS);
+        ColCoef<T, V> kc;
+#pragma unroll
+        for (int e = 0; e < V; ++e) kc.k[e] = d2_coef<T, ADJ>(j0 + e, W);
+        Pack<T, V> m = row_load<T, V>(x, r0 - 1, H, W, j0);
+        Pack<T, V> c = row_load<T, V>(x, r0, H, W, j0);
+        for (int i0 = r0; i0 < r1; i0 += GRAD_GROUP) {
+            Pack<T, V> nx[GRAD_GROUP];
+#pragma unroll
+            for (int g = 0; g < GRAD_GROUP; ++g) nx[g] = row_load<T, V>(x, i0 + g + 1, H, W, j0);
+#pragma unroll
+            for (int g = 0; g < GRAD_GROUP; ++g) {
+                const int i = i0 + g;
+                if (i < r1) {
+                    const Pack<T, V> a = row_stencil<T, V>(m, c, nx[g], d2_coef<T, ADJ>(i, H));
+                    T l, r;
+                    row_neighbours<T, V>(x + (int64_t)i * W, c, j0, W, lane, l, r);
+                    const Pack<T, V> b = col_stencil<T, V>(c, l, r, kc);
+                    Pack<T, V> o;
+#pragma unroll
+                    for (int e = 0; e < V; ++e) o.v[e] = w0ih * a.v[e] + w1ih * b.v[e];
+                    pack_store<T, V>(out + (int64_t)i * W, j0, W, o);
+                }
+                m = c;
+                c = nx[g];
+            }
+        }
+    }
+}
+// edge=True: the pixels within 3 samples of an image edge, exactly as the scalar kernel computes them
+template <typename T, bool ADJ>
+__global__ void __launch_bounds__(DF_BLOCK) lap2d_frame_kernel(T* __restrict__ out, const T* __restrict__ x, int64_t H,
+                                                               int64_t W, T w0ih, T w1ih) {
+    const int64_t nrow = 6 * W, total = nrow + 6 * H, stride = (int64_t)gridDim.x * DF_BLOCK;
+    for (int64_t q = (int64_t)blockIdx.x * DF_BLOCK + threadIdx.x; q < total; q += stride) {
+        int64_t r, c;
+        if (q < nrow) {
+            const int64_t k = q / W;
+            c = q - k * W;
+            r = k < 3 ? k : H - 6 + k;
+        } else {
+            const int64_t k = (q - nrow) / H;
+            r = (q - nrow) - k * H;
+            c = k < 3 ? k : W - 6 + k;
+        }
+        if (r < 0 || r >= H || c < 0 || c >= W) continue;
+        const int64_t f = r * W + c;
+        const T a = ADJ ? d2_adj<T>(x + f, r, H, W, 1, T(1)) : d2_fwd<T>(x + f, r, H, W, 1, T(1));
+        const T b = ADJ ? d2_adj<T>(x + f, c, W, 1, 1, T(1)) : d2_fwd<T>(x + f, c, W, 1, 1, T(1));
+        out[f] = w0ih * a + w1ih * b;
+    }
+}
+
 template <typename T, bool ADJ>
 static int lap2d_launch(T* out, const T* x, int64_t H, int64_t W, double w0, double w1, double s0, double s1, int edge,
                         cudaStream_t s, const char* what) {
@@ -239,8 +425,22 @@ static int lap2d_launch(T* out, const T* x, int64_t H, int64_t W, double w0, dou
     if (H * W == 0) return PCS_OK;
     PCS_REQUIRE(out && x && out != x, "%s: null or aliased pointer", what);
     PCS_REQUIRE(!edge || (H >= 3 && W >= 3), "%s: edge=True needs >= 3 samples per axis", what);
-    lap2d_kernel<T, ADJ><<<grid_for(H * W, DF_BLOCK, DF_CTAS_PER_SM), DF_BLOCK, 0, s>>>(
-        out, x, H, W, edge, (T)(w0 / (s0 * s0)), (T)(w1 / (s1 * s1)));
+    const T a0 = (T)(w0 / (s0 * s0)), a1 = (T)(w1 / (s1 * s1));
+    if (H < (1ll << 31) - 64 && W < (1ll << 31) - 4096 && (!edge || (H >= 6 && W >= 6))) {
+        constexpr int VEC = 16 / (int)sizeof(T);
+        if (t2_vec_ok<T>(W, {out, x})) {
+            const Tiles tl = tiles_of<VEC>((int)H, (int)W);
+            const int grid = (int)std::min<long long>(tl.n, (long long)num_sms() * T2_GRID_PER_SM);
+            lap2d_tiled_kernel<T, VEC, ADJ><<<grid, T2_BLOCK, 0, s>>>(out, x, (int)H, (int)W, a0, a1);
+        } else {
+            const Tiles tl = tiles_of<1>((int)H, (int)W);
+            const int grid = (int)std::min<long long>(tl.n, (long long)num_sms() * T2_GRID_PER_SM);
+            lap2d_tiled_kernel<T, 1, ADJ><<<grid, T2_BLOCK, 0, s>>>(out, x, (int)H, (int)W, a0, a1);
+        }
+        if (edge) lap2d_frame_kernel<T, ADJ><<<grid_for(6 * (H + W), DF_BLOCK, DF_CTAS_PER_SM), DF_BLOCK, 0, s>>>(out, x, H, W, a0, a1);
+        return check_launch(what);
+    }
+    lap2d_kernel<T, ADJ><<<grid_for(H * W, DF_BLOCK, DF_CTAS_PER_SM), DF_BLOCK, 0, s>>>(out, x, H, W, edge, a0, a1);
     return check_launch(what);
 }
 #define LAP_PARAMS                                                                                              \

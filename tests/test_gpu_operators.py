@@ -22,7 +22,8 @@ def rng(seed=0):
 @pytest.mark.parametrize('dtype,tol', DT)
 @pytest.mark.parametrize('kind', ['forward', 'centered', 'backward'])
 @pytest.mark.parametrize('edge', [True, False])
-@pytest.mark.parametrize('shape,axis', [(None, 0), ((7, 9), 0), ((7, 9), 1), ((4, 5, 6), 1), ((4, 5, 6), -1), ((2, 3), 0)])
+@pytest.mark.parametrize('shape,axis', [(None, 0), ((7, 9), 0), ((7, 9), 1), ((4, 5, 6), 1), ((4, 5, 6), -1), ((2, 3), 0),
+                                        ((40, 520), 0), ((40, 520), 1), ((3, 20, 132), 1), ((2050,), 0)])
 def test_first_derivative(dtype, tol, kind, edge, shape, axis):
     from pycsou_b200.linop.diff import FirstDerivative
     n = 37 if shape is None else int(np.prod(shape))
@@ -68,10 +69,13 @@ def test_gradient(dtype, tol, kind, shape):
 
 @pytest.mark.parametrize('dtype,tol', DT)
 @pytest.mark.parametrize('edge', [True, False])
-def test_laplacian(dtype, tol, edge):
+@pytest.mark.parametrize('shape', [(19, 33), (70, 1028), (6, 6), (5, 40), (3, 3), (130, 516)])
+def test_laplacian(dtype, tol, edge, shape):
+    """(19, 33): scalar tiles; (70, 1028), (130, 516): vector tiles, several tiles per row; (6, 6): smallest image on the
+    tiled path with edge rows; (5, 40), (3, 3): scalar fallback kernel."""
     from pycsou_b200.linop.diff import Laplacian
-    shape = (19, 33)
-    x, z = rng(1).standard_normal(19 * 33).astype(dtype), rng(2).standard_normal(19 * 33).astype(dtype)
+    n = shape[0] * shape[1]
+    x, z = rng(1).standard_normal(n).astype(dtype), rng(2).standard_normal(n).astype(dtype)
     L = Laplacian(shape, weights=(1.5, 0.5), step=(1., 2.), edge=edge, dtype=np.dtype(dtype).name)
     Lo = O.Laplacian(shape, weights=(1.5, 0.5), step=(1., 2.), edge=edge)
     assert rel_l2(L(x), Lo.matvec(x.astype(np.float64))) < tol
