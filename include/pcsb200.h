@@ -189,7 +189,7 @@ int pcs_mask_to_indices_static(const void* mask_u8, int64_t n, void* total_out_i
  *   workspace: pcs_pds_tv_workspace_bytes() bytes, zero-initialised once. */
 int64_t pcs_pds_tv_workspace_bytes(void);
 /* What the last pcs_pds_tv_step / _run / _step_slab call of the calling host thread launched (HOST int64[8]):
- * {kernel (0 single-role, 1 warp-specialised), blocks, threads per block, dynamic shared memory, strips,
+ * {kernel (0 single-role, 1 warp-specialised, 2 persistent multi-update), blocks, threads per block, dynamic shared memory, strips,
  *  output columns per strip, long segments of the uneven one-wave split (-1: even split), TMA staging used}.
  * Diagnostic only: the parity tests assert that the benchmarked kernel and geometry are the ones under test. */
 int pcs_pds_tv_last_launch(int64_t* out8_host);
@@ -205,6 +205,9 @@ PCS_DECL_REAL(pcs_pds_tv_step,
  * and puts its four sums in row k of diag_out_f64 (n_iters x 4 doubles).  The result is in pair a when n_iters is even.
  * For the part of GenericIterativeAlgorithm.iterate (core/solver.py:64-76) in which no stop test can fire (up to
  * min_iter).  Not for data_mode 3. */
+/* (pcs_pds_tv_run: when the 7 N s working set stays in L2 -- <= 96 MB -- and there is no convolution, all n_iters updates
+ * run in ONE cooperative launch of a persistent kernel with a grid-wide barrier between updates; results are bit-identical
+ * to n_iters single launches.  PCS_PDS_PERSIST=0 / 1 in the environment forces it off / on.) */
 PCS_DECL_REAL(pcs_pds_tv_run,
               (void* x_a, void* z_a, void* x_b, void* z_b, const void* b, int64_t H, int64_t W, int data_mode, int ntaps,
                const double* crow_host, const double* ccol_host, const void* edge, int nl, int nr, int nt, int nb,

@@ -24,4 +24,5 @@ def run(dtype, size=4096):
     m = pt[:, :9].mean(0)
     for k, n in enumerate(NAMES):
         print(f'   {n:14s} mean {m[k]:9.0f} cyc  {100 * m[k] / tot.mean():5.1f}%')
-run('f32'); run('f64')
+size = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
+run('f32', size); run('f64', size)

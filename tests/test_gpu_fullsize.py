@@ -125,7 +125,8 @@ def test_c2_tv_denoise_1024(dtype):
     assert abs(s.tau - 0.3) < 0.05 and s.tau == s.sigma            # proxalgs.py:286-287 with beta = 1, L = sqrt(8)
     est, _, diag = s.iterate()
     L = m['last_launch']()
-    assert L['kernel'] == 'pds_tv_kernel' and L['use_tma'] == 1 and L['strips'] == 9
+    # 1024^2 is L2-resident: the 20 updates run in one cooperative launch of the persistent kernel
+    assert L['kernel'] == 'pds_tv_persist_kernel' and L['use_tma'] == 1 and L['strips'] == 9
     ex, ez = rel_l2(est['primal_variable'], xo), rel_l2(est['dual_variable'], zo)
     print(f'1024^2 {dtype}, {k} updates: rel-L2 x {ex:.2e}, z {ez:.2e}, launch {L}')
     if dtype == 'float64':
@@ -187,3 +188,23 @@ def test_one_wave_uneven_split_geometry_on_a_small_image(dtype, nsm, monkeypatch
             assert L['n_fast'] >= 0                       # uneven split + companion search were exercised
     assert np.array_equal(est['primal_variable'], base['primal_variable'])
     assert np.array_equal(est['dual_variable'], base['dual_variable'])
+
+
+@pytest.mark.parametrize('dtype', ['float64', 'float32'])
+@pytest.mark.parametrize('shape,data', [((1024, 1024), 'identity'), ((300, 520), 'none'), ((64, 136), 'identity')])
+def test_persistent_multi_update_kernel_is_bit_identical(shape, data, dtype, monkeypatch):
+    """pcs_pds_tv_run: all updates in one cooperative launch (grid barrier between updates) vs one launch per update --
+    identical iterates and identical diagnostics rows, for odd and even update counts."""
+    from tests.test_gpu_fused import _problem, _run
+    m = _mods()
+    kw = _problem(shape, data, 'nonneg', 'l21', dtype)
+    for k in (2, 7):
+        monkeypatch.setenv('PCS_PDS_PERSIST', '0')
+        _, ref, dref = _run(kw, k, True)
+        assert m['last_launch']()['kernel'] == 'pds_tv_kernel'
+        monkeypatch.setenv('PCS_PDS_PERSIST', '1')
+        _, est, dest = _run(kw, k, True)
+        assert m['last_launch']()['kernel'] == 'pds_tv_persist_kernel'
+        assert np.array_equal(est['primal_variable'], ref['primal_variable'])
+        assert np.array_equal(est['dual_variable'], ref['dual_variable'])
+        assert np.array_equal(dest.to_numpy(dtype=float), dref.to_numpy(dtype=float))
