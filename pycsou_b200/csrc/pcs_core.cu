@@ -120,7 +120,26 @@ __global__ void __launch_bounds__(EW_BLOCK) ew_kernel(T* __restrict__ out, const
     const int64_t stride = (int64_t)gridDim.x * EW_BLOCK;
     if (vec_ok) {
         const int64_t nv = n / VN;
-        for (int64_t i = tid; i < nv; i += stride) {
+        int64_t i = tid;
+        if (NIN == 1) {
+            // one-operand kernels: two independent 16-byte loads in flight per thread (one kept them at 4.6-5.4 TB/s)
+            for (; i + stride < nv; i += 2 * stride) {
+                const V v0 = reinterpret_cast<const V*>(x)[i], v1 = reinterpret_cast<const V*>(x)[i + stride];
+                V o0, o1;
+                const T* p0 = reinterpret_cast<const T*>(&v0);
+                const T* p1 = reinterpret_cast<const T*>(&v1);
+                T* q0 = reinterpret_cast<T*>(&o0);
+                T* q1 = reinterpret_cast<T*>(&o1);
+#pragma unroll
+                for (int k = 0; k < VN; ++k) {
+                    q0[k] = ew_apply<T, OP>(p0[k], p0[k], p0[k], a, b, c);
+                    q1[k] = ew_apply<T, OP>(p1[k], p1[k], p1[k], a, b, c);
+                }
+                reinterpret_cast<V*>(out)[i] = o0;
+                reinterpret_cast<V*>(out)[i + stride] = o1;
+            }
+        }
+        for (; i < nv; i += stride) {
             V vx = reinterpret_cast<const V*>(x)[i], vy = vx, vz = vx, vo;
             if (NIN > 1) vy = reinterpret_cast<const V*>(y)[i];
             if (NIN > 2) vz = reinterpret_cast<const V*>(z)[i];
@@ -132,8 +151,8 @@ __global__ void __launch_bounds__(EW_BLOCK) ew_kernel(T* __restrict__ out, const
             for (int k = 0; k < VN; ++k) po[k] = ew_apply<T, OP>(px[k], py[k], pz[k], a, b, c);
             reinterpret_cast<V*>(out)[i] = vo;
         }
-        for (int64_t i = nv * VN + tid; i < n; i += stride)
-            out[i] = ew_apply<T, OP>(x[i], NIN > 1 ? y[i] : T(0), NIN > 2 ? z[i] : T(0), a, b, c);
+        for (int64_t r = nv * VN + tid; r < n; r += stride)
+            out[r] = ew_apply<T, OP>(x[r], NIN > 1 ? y[r] : T(0), NIN > 2 ? z[r] : T(0), a, b, c);
     } else {
         for (int64_t i = tid; i < n; i += stride)
             out[i] = ew_apply<T, OP>(x[i], NIN > 1 ? y[i] : T(0), NIN > 2 ? z[i] : T(0), a, b, c);
@@ -247,11 +266,49 @@ __global__ void __launch_bounds__(EW_BLOCK) prox_l21_kernel(T* __restrict__ out,
     }
 }
 
+// real planes, every plane 16-byte aligned: a thread owns Vec<T>::N consecutive groups (16-byte loads and stores)
+template <typename T, int C>
+__global__ void __launch_bounds__(EW_BLOCK) prox_l21_vec_kernel(T* __restrict__ out, const T* __restrict__ x, T tau,
+                                                                int64_t G) {
+    typedef typename Vec<T>::type VT;
+    constexpr int V = Vec<T>::N;
+    const int64_t stride = (int64_t)gridDim.x * EW_BLOCK, Gv = G / V;
+    for (int64_t p = (int64_t)blockIdx.x * EW_BLOCK + threadIdx.x; p < Gv; p += stride) {
+        T v[C][V], ss[V];
+#pragma unroll
+        for (int c = 0; c < C; ++c) *reinterpret_cast<VT*>(v[c]) = reinterpret_cast<const VT*>(x + (int64_t)c * G)[p];
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+            ss[k] = T(0);
+#pragma unroll
+            for (int c = 0; c < C; ++c) ss[k] += v[c][k] * v[c][k];
+        }
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+            const T f = l21_factor<T>(tsqrt<T>(ss[k]), tau);
+#pragma unroll
+            for (int c = 0; c < C; ++c) v[c][k] = f * v[c][k];
+        }
+#pragma unroll
+        for (int c = 0; c < C; ++c) reinterpret_cast<VT*>(out + (int64_t)c * G)[p] = *reinterpret_cast<const VT*>(v[c]);
+    }
+}
+
 template <typename T>
 static int pcs_prox_l21_impl(T* out, const T* x, T tau, int64_t G, int C, int cplx, cudaStream_t s) {
     PCS_REQUIRE(G >= 0 && C >= 1 && C <= 4, "pcs_prox_l21: need 1 <= n_comp <= 4 (got %d)", C);
     if (G == 0) return PCS_OK;
     PCS_REQUIRE(out && x, "pcs_prox_l21: null pointer");
+    if (!cplx && G % Vec<T>::N == 0 && aligned16(out) && aligned16(x)) {
+        const int gridv = grid_for(G / Vec<T>::N, EW_BLOCK, EW_CTAS_PER_SM);
+        switch (C) {
+            case 1: prox_l21_vec_kernel<T, 1><<<gridv, EW_BLOCK, 0, s>>>(out, x, tau, G); break;
+            case 2: prox_l21_vec_kernel<T, 2><<<gridv, EW_BLOCK, 0, s>>>(out, x, tau, G); break;
+            case 3: prox_l21_vec_kernel<T, 3><<<gridv, EW_BLOCK, 0, s>>>(out, x, tau, G); break;
+            default: prox_l21_vec_kernel<T, 4><<<gridv, EW_BLOCK, 0, s>>>(out, x, tau, G); break;
+        }
+        return check_launch("pcs_prox_l21");
+    }
     int grid = grid_for(G, EW_BLOCK, EW_CTAS_PER_SM);
     switch (C) {
         case 1: prox_l21_kernel<T, 1><<<grid, EW_BLOCK, 0, s>>>(out, x, tau, G, cplx); break;
@@ -276,38 +333,80 @@ extern "C" int64_t pcs_reduce_workspace_bytes(void) {
     return (int64_t)(4 * (int64_t)pcs::num_sms() * 8 + 16) * 8;
 }
 
+// one term of the sum (a = x[i], d = y[i] where the reduction has a second operand)
+template <int OP> __device__ __forceinline__ double rd_term(double a, double d) {
+    if (OP == RD_SUMSQ) return a * a;
+    if (OP == RD_DIFFSUMSQ) { const double t = a - d; return t * t; }
+    if (OP == RD_SUMABS) return fabs(a);
+    if (OP == RD_DOT) return a * d;
+    if (OP == RD_NEGLOG) return a > 0.0 ? -log(a) : INFINITY;                       // func/penalty.py:819-822
+    if (OP == RD_XLOGX) return a > 0.0 ? a * log(a) : (a == 0.0 ? 0.0 : INFINITY);  // func/penalty.py:899-903
+    if (OP == RD_KL) {                                                              // func/loss.py:659-664
+        const double z = (a > 0.0 && d > 0.0) ? d * log(d / a) : ((a == 0.0 && d >= 0.0) ? 0.0 : INFINITY);
+        return z - d + a;
+    }
+    return 0.0;
+}
+template <int OP> constexpr bool rd_binary() { return OP == RD_DIFFSUMSQ || OP == RD_DOT || OP == RD_KL; }
+
+// Grid-stride sum in double.  With 16-byte aligned operands a thread loads RD_U x 16 bytes per operand and trip (all
+// loads issued before the first use) and keeps RD_U independent accumulation chains: with one 4-byte load and one chain
+// per trip the fp32 sum of squares ran at 3.4 TB/s (profiles/r02_probe_ops.txt).
+constexpr int RD_U = 4;
 template <typename T, int OP>
 __global__ void __launch_bounds__(RD_BLOCK) reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, int64_t n,
-                                                          double* __restrict__ out, double* partials,
+                                                          int vec_ok, double* __restrict__ out, double* partials,
                                                           unsigned int* ticket) {
     __shared__ double sm[RD_BLOCK / 32];
+    typedef typename Vec<T>::type VT;
+    constexpr int V = Vec<T>::N;
     const int64_t stride = (int64_t)gridDim.x * RD_BLOCK;
-    double acc[1] = {0.0};
-    for (int64_t i = (int64_t)blockIdx.x * RD_BLOCK + threadIdx.x; i < n; i += stride) {
-        double a = (double)x[i];
-        if (OP == RD_SUMSQ) acc[0] += a * a;
-        if (OP == RD_DIFFSUMSQ) { double d = a - (double)y[i]; acc[0] += d * d; }
-        if (OP == RD_SUMABS) acc[0] += fabs(a);
-        if (OP == RD_DOT) acc[0] += a * (double)y[i];
-        if (OP == RD_NEGLOG) acc[0] += a > 0.0 ? -log(a) : INFINITY;                       // func/penalty.py:819-822
-        if (OP == RD_XLOGX) acc[0] += a > 0.0 ? a * log(a) : (a == 0.0 ? 0.0 : INFINITY);  // func/penalty.py:899-903
-        if (OP == RD_KL) {                                                                 // func/loss.py:659-664
-            const double d = (double)y[i];
-            const double z = (a > 0.0 && d > 0.0) ? d * log(d / a) : ((a == 0.0 && d >= 0.0) ? 0.0 : INFINITY);
-            acc[0] += z - d + a;
+    const int64_t gtid = (int64_t)blockIdx.x * RD_BLOCK + threadIdx.x;
+    double acc[RD_U];
+#pragma unroll
+    for (int u = 0; u < RD_U; ++u) acc[u] = 0.0;
+    int64_t done = 0;                      // elements [0, done) are covered by the vector loop
+    if (vec_ok) {
+        const int64_t nv = n / V;
+        const VT* __restrict__ xv = reinterpret_cast<const VT*>(x);
+        const VT* __restrict__ yv = reinterpret_cast<const VT*>(y);
+        for (int64_t i0 = gtid; i0 < nv; i0 += RD_U * stride) {
+            T a[RD_U][V], d[RD_U][V];
+#pragma unroll
+            for (int u = 0; u < RD_U; ++u) {
+                const int64_t i = i0 + u * stride;
+                if (i < nv) {
+                    *reinterpret_cast<VT*>(a[u]) = xv[i];
+                    if (rd_binary<OP>()) *reinterpret_cast<VT*>(d[u]) = yv[i];
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < RD_U; ++u) {
+                if (i0 + u * stride < nv) {
+#pragma unroll
+                    for (int e = 0; e < V; ++e)
+                        acc[u] += rd_term<OP>((double)a[u][e], rd_binary<OP>() ? (double)d[u][e] : 0.0);
+                }
+            }
         }
+        done = nv * V;
     }
-    grid_sum_finish<1, RD_BLOCK>(acc, partials, ticket, out, sm);
+    for (int64_t i = done + gtid; i < n; i += stride)
+        acc[0] += rd_term<OP>((double)x[i], rd_binary<OP>() ? (double)y[i] : 0.0);
+    static_assert(RD_U == 4, "the final sum below is written for four chains");
+    double tot[1] = {(acc[0] + acc[1]) + (acc[2] + acc[3])};
+    grid_sum_finish<1, RD_BLOCK>(tot, partials, ticket, out, sm);
 }
 
 template <typename T, int OP>
 static int reduce_launch(const T* x, const T* y, int64_t n, double* out, void* ws, cudaStream_t s, const char* what) {
     PCS_REQUIRE(n >= 0 && out && ws, "%s: bad arguments", what);
     PCS_REQUIRE(n == 0 || (x && ((OP != RD_DIFFSUMSQ && OP != RD_DOT && OP != RD_KL) || y)), "%s: null pointer", what);
-    int grid = grid_for(n, RD_BLOCK, RD_CTAS_PER_SM);
+    const int vec_ok = ((uintptr_t)x % 16 == 0) && (y == nullptr || (uintptr_t)y % 16 == 0);
+    int grid = grid_for(vec_ok ? (n + Vec<T>::N - 1) / Vec<T>::N : n, RD_BLOCK, RD_CTAS_PER_SM);
     double* partials = (double*)ws;
     unsigned int* ticket = (unsigned int*)(partials + 4 * (int64_t)pcs::num_sms() * 8);
-    reduce_kernel<T, OP><<<grid, RD_BLOCK, 0, s>>>(x, y, n, out, partials, ticket);
+    reduce_kernel<T, OP><<<grid, RD_BLOCK, 0, s>>>(x, y, n, vec_ok, out, partials, ticket);
     return check_launch(what);
 }
 
@@ -436,7 +535,8 @@ PCS_EXPORT_REAL(pcs_threshold_newton_step,
 // sum over groups of the group 2-norm, planes layout (L21Norm.__call__, func/penalty.py:548-549)
 template <typename T>
 __global__ void __launch_bounds__(RD_BLOCK) sumgroupnorm_kernel(const T* __restrict__ x, int64_t G, int C, int cplx,
-                                                                double* out, double* partials, unsigned int* ticket) {
+                                                                int vec_ok, double* out, double* partials,
+                                                                unsigned int* ticket) {
     __shared__ double sm[RD_BLOCK / 32];
     const int64_t stride = (int64_t)gridDim.x * RD_BLOCK;
     const int64_t e = cplx ? 2 : 1;
@@ -444,6 +544,41 @@ __global__ void __launch_bounds__(RD_BLOCK) sumgroupnorm_kernel(const T* __restr
     // group norm in the working precision (as np.linalg.norm of a float32 group is), sum over groups in double; the fp64
     // square root per group of the all-double version made this kernel compute bound (1.07 TB/s in fp32)
     constexpr int U = 4;                   // groups per thread and trip: U x C independent loads in flight
+    if (vec_ok) {
+        // real planes with 16-byte aligned rows: a thread owns V consecutive groups (one 16-byte load per plane) and
+        // two such packs per trip
+        typedef typename Vec<T>::type VT;
+        constexpr int V = Vec<T>::N, UV = 2;
+        const int64_t Gv = G / V;
+        for (int64_t p0 = (int64_t)blockIdx.x * RD_BLOCK + threadIdx.x; p0 < Gv; p0 += UV * stride) {
+            T ss[UV][V];
+#pragma unroll
+            for (int u = 0; u < UV; ++u)
+#pragma unroll
+                for (int k = 0; k < V; ++k) ss[u][k] = T(0);
+            for (int c = 0; c < C; ++c) {
+                T v[UV][V];
+#pragma unroll
+                for (int u = 0; u < UV; ++u) {
+                    const int64_t pp = p0 + u * stride;
+                    if (pp < Gv) *reinterpret_cast<VT*>(v[u]) = reinterpret_cast<const VT*>(x + (int64_t)c * G)[pp];
+                    else
+#pragma unroll
+                        for (int k = 0; k < V; ++k) v[u][k] = T(0);
+                }
+#pragma unroll
+                for (int u = 0; u < UV; ++u)
+#pragma unroll
+                    for (int k = 0; k < V; ++k) ss[u][k] = fma(v[u][k], v[u][k], ss[u][k]);
+            }
+#pragma unroll
+            for (int u = 0; u < UV; ++u)
+#pragma unroll
+                for (int k = 0; k < V; ++k) acc[0] += (double)tsqrt<T>(ss[u][k]);
+        }
+        grid_sum_finish<1, RD_BLOCK>(acc, partials, ticket, out, sm);
+        return;
+    }
     for (int64_t g0 = (int64_t)blockIdx.x * RD_BLOCK + threadIdx.x; g0 < G; g0 += U * stride) {
         T ss[U];
 #pragma unroll
@@ -468,10 +603,12 @@ __global__ void __launch_bounds__(RD_BLOCK) sumgroupnorm_kernel(const T* __restr
 template <typename T>
 static int pcs_reduce_sumgroupnorm_impl(const T* x, int64_t G, int C, int cplx, double* out, void* ws, cudaStream_t s) {
     PCS_REQUIRE(G >= 0 && C >= 1 && out && ws && (G == 0 || x), "pcs_reduce_sumgroupnorm: bad arguments");
-    int grid = grid_for(G, RD_BLOCK, RD_CTAS_PER_SM);
+    // vector path: real data, every plane 16-byte aligned and a whole number of vectors long
+    const int vec_ok = !cplx && G > 0 && ((uintptr_t)x % 16 == 0) && (G % Vec<T>::N == 0);
+    int grid = grid_for(vec_ok ? G / Vec<T>::N : G, RD_BLOCK, RD_CTAS_PER_SM);
     double* partials = (double*)ws;
     unsigned int* ticket = (unsigned int*)(partials + 4 * (int64_t)pcs::num_sms() * 8);
-    sumgroupnorm_kernel<T><<<grid, RD_BLOCK, 0, s>>>(x, G, C, cplx, out, partials, ticket);
+    sumgroupnorm_kernel<T><<<grid, RD_BLOCK, 0, s>>>(x, G, C, cplx, vec_ok, out, partials, ticket);
     return check_launch("pcs_reduce_sumgroupnorm");
 }
 PCS_EXPORT_REAL(pcs_reduce_sumgroupnorm,
