@@ -373,6 +373,172 @@ __global__ void __launch_bounds__(C2_BX * C2_BY) conv2d_sep_kernel(T* __restrict
     }
 }
 
+// ---- streaming form of the separable kernel (odd square-ish filters up to 15 taps per axis) -------------------------
+// The tile kernel above re-reads a (32 + kh - 1) x (64 + kw - 1) halo tile per 32 x 64 outputs, stages it with one integer
+// division per element and spends one shared-memory load per multiply-add in its row pass: ~1 TB/s at 4096^2.  Here a
+// block owns a strip of 128 output columns and MARCHES down a segment of rows, 8 input rows per step:
+//   global rows -> registers (the loads of step t + 1 are in flight while step t is filtered) -> shared stage ->
+//   row pass (a thread filters 4 adjacent outputs of one row from an 18-sample register window, 128-bit conflict-free
+//   shared loads) -> ring of row-filtered lines -> column pass (thread <-> column, 4 rows) -> global.
+// Every input row is read once per strip (+ kh - 1 rows per segment), nothing is recomputed vertically.  KH / KW are the
+// exact tap counts (compile time), so an output accumulates exactly its taps, in ascending order, with one fma each --
+// the same operations in the same order as the tile kernel.
+constexpr int CS_TC = 128;              // output columns per strip
+constexpr int CS_BR = 8;                // input rows per step
+constexpr int CS_RUN = 4;               // row-pass outputs per thread
+constexpr int CS_RG = 4;                // column-pass outputs per thread
+constexpr int CS_NT = 256;
+template <typename T> constexpr int cs_pitch(int n) {                  // smallest pitch >= n with pitch bytes = 16 mod 128
+    const int per16 = 16 / (int)sizeof(T), per128 = 128 / (int)sizeof(T);
+    int p = (n + per16 - 1) / per16 * per16;
+    while (p % per128 != per16) p += per16;
+    return p;
+}
+template <typename T, int K> struct CsGeo {
+    static constexpr int SW = CS_TC + K - 1;                      // staged columns
+    static constexpr int PX = cs_pitch<T>(SW + 3);                // (+3: the row-pass window is read in whole vectors)
+    static constexpr int PM = cs_pitch<T>(CS_TC);
+    static constexpr int NB = (CS_BR + K - 1 + CS_BR - 1) / CS_BR;  // ring boxes of CS_BR rows
+    static constexpr int RING = NB * CS_BR;
+    static constexpr int LAG = NB - 1;                            // output box s is complete after load step s + LAG
+    static constexpr int NLD = (CS_BR * SW + CS_NT - 1) / CS_NT;  // staged elements per thread and step
+    static constexpr int KT = (K + 3) / 4 * 4;                    // taps per axis in shared memory (padded)
+    static constexpr size_t SMEM = ((size_t)2 * CS_BR * PX + (size_t)RING * PM + 2 * KT) * sizeof(T);
+};
+
+template <typename T, int K>
+__global__ void __launch_bounds__(CS_NT) conv2d_sep_stream_kernel(T* __restrict__ out, const T* __restrict__ x,
+                                                                   const T* __restrict__ hcol,
+                                                                   const T* __restrict__ hrow, int sgn, int ca, int cb,
+                                                                   const T* __restrict__ sub, int H, int W, int seg_rows) {
+    using G = CsGeo<T, K>;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* const stage = reinterpret_cast<T*>(smem_raw);               // 2 x CS_BR x PX
+    T* const ring = stage + 2 * CS_BR * G::PX;                     // RING x PM
+    T* const s_col = ring + G::RING * G::PM;                       // taps in correlation order (the device arrays hold them
+    T* const s_row = s_col + G::KT;                                // in convolution order): read back into registers per pass
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < K) {
+        s_col[tid] = (sgn > 0) ? hcol[tid] : hcol[K - 1 - tid];
+        s_row[tid] = (sgn > 0) ? hrow[tid] : hrow[K - 1 - tid];
+    }
+    const int c0 = (int)blockIdx.x * CS_TC;
+    const int ra = (int)blockIdx.y * seg_rows, rb = min(H, ra + seg_rows);
+    if (ra >= rb) return;
+    const int nout = (rb - ra + CS_BR - 1) / CS_BR;               // output boxes
+    const int nloop = nout + G::LAG;
+
+    // staging: element e of a step = (row e / SW, column e % SW) of the box whose corner is (ra - ca + 8 t, c0 - cb)
+    T regs[G::NLD];
+    auto gload = [&](int t) {
+        const int r0 = ra - ca + CS_BR * t;
+#pragma unroll
+        for (int k = 0; k < G::NLD; ++k) {
+            const int e = tid + k * CS_NT;
+            const int lr = e / G::SW, lc = e - lr * G::SW;
+            const int r = r0 + lr, c = c0 - cb + lc;
+            regs[k] = (e < CS_BR * G::SW && r >= 0 && r < H && c >= 0 && c < W) ? x[(int64_t)r * W + c] : T(0);
+        }
+    };
+    auto sstore = [&](int t) {
+        T* st = stage + (t & 1) * CS_BR * G::PX;
+#pragma unroll
+        for (int k = 0; k < G::NLD; ++k) {
+            const int e = tid + k * CS_NT;
+            const int lr = e / G::SW, lc = e - lr * G::SW;
+            if (e < CS_BR * G::SW) st[lr * G::PX + lc] = regs[k];
+        }
+    };
+    // row pass: lanes 0-7 of a quarter warp are the 8 rows of the step (same columns): conflict-free 128-bit loads
+    const int prow = lane & (CS_BR - 1), jc = (warp * (32 / CS_BR) + lane / CS_BR) * CS_RUN;
+    constexpr int VN = Vec<T>::N;
+    constexpr int WIN = (CS_RUN + K - 1 + VN - 1) / VN * VN;
+    typedef typename Vec<T>::type VT;
+    // column pass: thread <-> (column j, rows [4 rg, 4 rg + 4) of the box)
+    const int j = tid & (CS_TC - 1), rg = tid >> 7;
+    const bool vcol = c0 + j < W;
+
+    gload(0);
+    for (int t = 0; t < nloop; ++t) {
+        sstore(t);
+        __syncthreads();                       // stage t complete; ring box t % NB free (its column pass ended last step)
+        if (t + 1 < nloop) gload(t + 1);
+        {
+            const T* xs = stage + (t & 1) * CS_BR * G::PX + prow * G::PX + jc;
+            T acc[CS_RUN], tr[K];
+#pragma unroll
+            for (int b = 0; b < K; ++b) tr[b] = s_row[b];
+#pragma unroll
+            for (int o = 0; o < CS_RUN; ++o) acc[o] = T(0);
+#pragma unroll
+            for (int k = 0; k < WIN; k += VN) {
+                T v[VN];
+                *reinterpret_cast<VT*>(v) = *reinterpret_cast<const VT*>(xs + k);
+#pragma unroll
+                for (int e = 0; e < VN; ++e) {
+#pragma unroll
+                    for (int o = 0; o < CS_RUN; ++o) {
+                        const int b = k + e - o;
+                        if (b >= 0 && b < K) acc[o] = fma(tr[b], v[e], acc[o]);
+                    }
+                }
+            }
+            T* dst = ring + ((t % G::NB) * CS_BR + prow) * G::PM + jc;
+#pragma unroll
+            for (int o = 0; o < CS_RUN; o += VN) *reinterpret_cast<VT*>(dst + o) = *reinterpret_cast<const VT*>(acc + o);
+        }
+        __syncthreads();                       // ring box t % NB complete
+        const int sbox = t - G::LAG;
+        if (sbox >= 0 && vcol) {
+            // output rows ra + 8 sbox + 4 rg + o need ring rows (relative to the segment's first staged row)
+            // 8 sbox + 4 rg + o + a, a < K
+            int rr = (sbox * CS_BR + CS_RG * rg) % G::RING;
+            T acc[CS_RG], tc[K];
+#pragma unroll
+            for (int a = 0; a < K; ++a) tc[a] = s_col[a];
+#pragma unroll
+            for (int o = 0; o < CS_RG; ++o) acc[o] = T(0);
+#pragma unroll
+            for (int k = 0; k < CS_RG + K - 1; ++k) {
+                const T m = ring[rr * G::PM + j];
+                rr = (rr + 1 == G::RING) ? 0 : rr + 1;
+#pragma unroll
+                for (int o = 0; o < CS_RG; ++o) {
+                    const int a = k - o;
+                    if (a >= 0 && a < K) acc[o] = fma(tc[a], m, acc[o]);
+                }
+            }
+            const int r0 = ra + sbox * CS_BR + CS_RG * rg;
+#pragma unroll
+            for (int o = 0; o < CS_RG; ++o) {
+                const int r = r0 + o;
+                if (r < rb) {
+                    const int64_t idx = (int64_t)r * W + c0 + j;
+                    out[idx] = sub ? acc[o] - sub[idx] : acc[o];
+                }
+            }
+        }
+    }
+}
+
+template <typename T, int K>
+static int conv2d_sep_stream_launch(T* out, const T* x, const T* hcol, const T* hrow, int off0, int off1, int sgn,
+                                    const T* sub, int64_t H, int64_t W, cudaStream_t s, const char* what) {
+    using G = CsGeo<T, K>;
+    const int ca = (sgn > 0) ? off0 : K - 1 - off0, cb = (sgn > 0) ? off1 : K - 1 - off1;
+    const int nstrips = (int)((W + CS_TC - 1) / CS_TC);
+    // ~4 blocks per SM; segments of at least 64 rows (the ring fill costs K - 1 extra rows per segment)
+    int nseg = (4 * num_sms() + nstrips - 1) / nstrips;
+    int seg_rows = (int)((H + nseg - 1) / nseg);
+    seg_rows = (seg_rows + CS_BR - 1) / CS_BR * CS_BR;
+    if (seg_rows < 64) seg_rows = 64;
+    nseg = (int)((H + seg_rows - 1) / seg_rows);
+    cudaFuncSetAttribute(conv2d_sep_stream_kernel<T, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
+    conv2d_sep_stream_kernel<T, K><<<dim3((unsigned)nstrips, (unsigned)nseg), CS_NT, G::SMEM, s>>>(
+        out, x, hcol, hrow, sgn, ca, cb, sub, (int)H, (int)W, seg_rows);
+    return check_launch(what);
+}
+
 template <typename T>
 static int conv2d_sep_launch(T* out, const T* x, const T* hcol, const T* hrow, int kh, int kw, int off0, int off1,
                              int sgn, const T* sub, int64_t H, int64_t W, cudaStream_t s, const char* what) {
@@ -380,6 +546,18 @@ static int conv2d_sep_launch(T* out, const T* x, const T* hcol, const T* hrow, i
     PCS_REQUIRE(off0 >= 0 && off0 < kh && off1 >= 0 && off1 < kw, "%s: offset outside the filter", what);
     if (H * W == 0) return PCS_OK;
     PCS_REQUIRE(out && x && hcol && hrow && out != x, "%s: null or aliased pointer", what);
+    static const bool stream_off = [] { const char* e = getenv("PCS_CONV2D_SEP_TILE"); return e && atoi(e) != 0; }();
+    if (kh == kw && (kh & 1) && kh >= 3 && kh <= 15 && H < (1ll << 31) - 64 && W < (1ll << 31) - 256 && !stream_off) {
+        switch (kh) {      // exact tap counts at compile time (PCS_CONV2D_SEP_TILE=1 keeps the tile kernel: A/B runs)
+            case 3: return conv2d_sep_stream_launch<T, 3>(out, x, hcol, hrow, off0, off1, sgn, sub, H, W, s, what);
+            case 5: return conv2d_sep_stream_launch<T, 5>(out, x, hcol, hrow, off0, off1, sgn, sub, H, W, s, what);
+            case 7: return conv2d_sep_stream_launch<T, 7>(out, x, hcol, hrow, off0, off1, sgn, sub, H, W, s, what);
+            case 9: return conv2d_sep_stream_launch<T, 9>(out, x, hcol, hrow, off0, off1, sgn, sub, H, W, s, what);
+            case 11: return conv2d_sep_stream_launch<T, 11>(out, x, hcol, hrow, off0, off1, sgn, sub, H, W, s, what);
+            case 13: return conv2d_sep_stream_launch<T, 13>(out, x, hcol, hrow, off0, off1, sgn, sub, H, W, s, what);
+            default: return conv2d_sep_stream_launch<T, 15>(out, x, hcol, hrow, off0, off1, sgn, sub, H, W, s, what);
+        }
+    }
     const size_t sh = C2_TH + kh - 1, sw = C2_TW + kw - 1;
     const size_t smem = ((size_t)kh + kw + sh * sw + sh * C2_TW) * sizeof(T);
     PCS_REQUIRE(smem <= C2_SMEM_LIMIT, "%s: filter %dx%d too large for the separable kernel", what, kh, kw);
