@@ -252,7 +252,8 @@ def last_launch():
     _lib.check(_lib.call_plain('pcs_pds_tv_last_launch', out.ctypes.data_as(C.c_void_p)))
     keys = ('kernel', 'blocks', 'threads', 'smem', 'strips', 'strip_cols', 'n_fast', 'use_tma')
     d = dict(zip(keys, (int(v) for v in out)))
-    d['kernel'] = {0: 'pds_tv_kernel', 1: 'pds_tv_ws_kernel', 2: 'pds_tv_persist_kernel'}.get(d['kernel'], 'none')
+    d['kernel'] = {0: 'pds_tv_kernel', 1: 'pds_tv_ws_kernel', 2: 'pds_tv_persist_kernel',
+                   3: 'pds_tv_resident_kernel'}.get(d['kernel'], 'none')
     return d
 
 

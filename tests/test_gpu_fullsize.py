@@ -125,8 +125,8 @@ def test_c2_tv_denoise_1024(dtype):
     assert abs(s.tau - 0.3) < 0.05 and s.tau == s.sigma            # proxalgs.py:286-287 with beta = 1, L = sqrt(8)
     est, _, diag = s.iterate()
     L = m['last_launch']()
-    # 1024^2 is L2-resident: the 20 updates run in one cooperative launch of the persistent kernel
-    assert L['kernel'] == 'pds_tv_persist_kernel' and L['use_tma'] == 1 and L['strips'] == 9
+    # x and z of a 1024^2 image fit in the SMs' shared memory: the 20 updates run on chip (one slab of 7 rows per SM)
+    assert L['kernel'] == 'pds_tv_resident_kernel' and L['blocks'] == 147 and L['threads'] == 512
     ex, ez = rel_l2(est['primal_variable'], xo), rel_l2(est['dual_variable'], zo)
     print(f'1024^2 {dtype}, {k} updates: rel-L2 x {ex:.2e}, z {ez:.2e}, launch {L}')
     if dtype == 'float64':
@@ -198,6 +198,7 @@ def test_persistent_multi_update_kernel_is_bit_identical(shape, data, dtype, mon
     from tests.test_gpu_fused import _problem, _run
     m = _mods()
     kw = _problem(shape, data, 'nonneg', 'l21', dtype)
+    monkeypatch.setenv('PCS_PDS_RESIDENT', '0')             # (the on-chip kernel would take these images: tested below)
     for k in (2, 7):
         monkeypatch.setenv('PCS_PDS_PERSIST', '0')
         _, ref, dref = _run(kw, k, True)
@@ -208,3 +209,49 @@ def test_persistent_multi_update_kernel_is_bit_identical(shape, data, dtype, mon
         assert np.array_equal(est['primal_variable'], ref['primal_variable'])
         assert np.array_equal(est['dual_variable'], ref['dual_variable'])
         assert np.array_equal(dest.to_numpy(dtype=float), dref.to_numpy(dtype=float))
+
+
+@pytest.mark.parametrize('dtype', ['float64', 'float32'])
+@pytest.mark.parametrize('shape,data,g,h', [((1024, 1024), 'identity', 'nonneg', 'l21'), ((300, 520), 'none', 'nonneg', 'l21'),
+                                            ((64, 136), 'identity', 'segment', 'l1'), ((1000, 700), 'identity', 'none', 'l21'),
+                                            ((5, 64), 'identity', 'nonneg', 'l21'), ((1036, 34), 'identity', 'l1', 'l21'),
+                                            ((149, 1024), 'identity', 'nonneg', 'l1')])
+def test_on_chip_resident_kernel_is_bit_identical(shape, data, g, h, dtype, monkeypatch):
+    """pcs_pds_tv_run on images whose x and z fit in shared memory (pds_tv_resident_kernel: one slab of rows per SM kept on
+    chip for all the updates, neighbours hand over boundary rows through global memory) vs one launch per update:
+    identical iterates for 2, 3 and 8 updates; the diagnostics sums agree to rounding (other summation order).  Shapes:
+    full slabs, a short last slab, one row per block, the tallest image that fits (fp64: 148 x 7 rows), two rows per slab."""
+    from tests.test_gpu_fused import _problem, _run
+    m = _mods()
+    if dtype == 'float64' and shape[0] > 148 * 7:
+        pytest.skip('taller than 148 slabs of 7 rows')
+    kw = _problem(shape, data, g, h, dtype)
+    for k in (2, 3, 8):
+        monkeypatch.setenv('PCS_PDS_RESIDENT', '0')
+        monkeypatch.setenv('PCS_PDS_PERSIST', '0')
+        _, ref, dref = _run(kw, k, True)
+        assert m['last_launch']()['kernel'] == 'pds_tv_kernel'
+        monkeypatch.setenv('PCS_PDS_RESIDENT', '1')
+        _, est, dest = _run(kw, k, True)
+        assert m['last_launch']()['kernel'] == 'pds_tv_resident_kernel'
+        assert np.array_equal(est['primal_variable'], ref['primal_variable'])
+        assert np.array_equal(est['dual_variable'], ref['dual_variable'])
+        a, b = dest.to_numpy(dtype=float), dref.to_numpy(dtype=float)
+        assert np.allclose(a, b, rtol=1e-11 if dtype == 'float64' else 2e-5, atol=0, equal_nan=True)
+
+
+def test_on_chip_resident_kernel_many_updates_in_chunks(monkeypatch):
+    """More updates than one launch of the resident kernel has room for in its per-update partial sums (65536 / 147 = 445 at
+    1024^2): the call is split into launches, each starting from the buffers the previous one left."""
+    from tests.test_gpu_fused import _problem, _run
+    m = _mods()
+    kw = _problem((1024, 1024), 'identity', 'nonneg', 'l21', 'float32')
+    monkeypatch.setenv('PCS_PDS_RESIDENT', '0')
+    monkeypatch.setenv('PCS_PDS_PERSIST', '0')
+    _, ref, dref = _run(kw, 451, True)
+    monkeypatch.setenv('PCS_PDS_RESIDENT', '1')
+    _, est, dest = _run(kw, 451, True)
+    assert m['last_launch']()['kernel'] == 'pds_tv_resident_kernel'
+    assert np.array_equal(est['primal_variable'], ref['primal_variable'])
+    assert np.array_equal(est['dual_variable'], ref['dual_variable'])
+    assert np.allclose(dest.to_numpy(dtype=float), dref.to_numpy(dtype=float), rtol=2e-5, atol=0, equal_nan=True)
