@@ -563,7 +563,7 @@ def c1_measure():
 
 
 def c2_measure():
-    """BASELINE.json configs[1]: TV denoising 1024^2, PDS, 200 updates, fp64 and fp32 (L2-resident working set)."""
+    """BASELINE.json configs[1]: TV denoising 1024^2, PDS, 200 updates, fp64 and fp32 (state resident on chip)."""
     import torch
     from pycsou_b200.func.loss import SquaredL2Loss
     from pycsou_b200.func.penalty import L21Norm, tv_groups
@@ -588,8 +588,10 @@ def c2_measure():
         gbs = alg / (ms_iter * 1e-3) / 1e9
         out[tag] = {'iter_per_s': 1e3 / ms_iter, 'us_per_update': 1e3 * ms_iter, 'effective_gbs': gbs,
                     'roofline_frac_L2_resident': gbs / peak, 'algorithmic_bytes': alg, 'kernel': last_launch()}
-    out['what'] = ('TV denoising 1024^2, 200 Condat-Vu updates per solve; the 7*N*s working set (59 / 29 MB) fits the '
-                   '126 MB L2, so the fraction is against the HBM figure but the traffic is L2-resident (latency bound)')
+    out['what'] = ('TV denoising 1024^2, 200 Condat-Vu updates per solve.  x and z (25 / 13 MB) stay in the shared memory '
+                   'of the 148 SMs for the whole solve (pds_tv_resident_kernel: a slab of 7 rows per SM, boundary rows '
+                   'handed over through L2); the "fraction" divides the 7*N*s bytes an update would move through HBM by '
+                   'the HBM figure -- no such traffic exists, the kernel is bound by the neighbour hand-over latency')
     return out
 
 

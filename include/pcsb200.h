@@ -207,7 +207,11 @@ PCS_DECL_REAL(pcs_pds_tv_step,
  * min_iter).  Not for data_mode 3. */
 /* (pcs_pds_tv_run: when the 7 N s working set stays in L2 -- <= 96 MB -- and there is no convolution, all n_iters updates
  * run in ONE cooperative launch of a persistent kernel with a grid-wide barrier between updates; results are bit-identical
- * to n_iters single launches.  PCS_PDS_PERSIST=0 / 1 in the environment forces it off / on.) */
+ * to n_iters single launches.  PCS_PDS_PERSIST=0 / 1 in the environment forces it off / on.
+ * Smaller still -- no convolution, W even and <= 1024, H <= 7 (f64) / 8 (f32) rows per SM, automatic geometry: x and z
+ * stay in the SMs' shared memory for the whole call (pds_tv_resident_kernel), x and z bit-identical to single launches,
+ * the sums of diag_out_f64 equal up to summation order; only the result pair is written in full, the other pair keeps
+ * whatever it held except for some boundary rows.  PCS_PDS_RESIDENT=0 switches it off.) */
 PCS_DECL_REAL(pcs_pds_tv_run,
               (void* x_a, void* z_a, void* x_b, void* z_b, const void* b, int64_t H, int64_t W, int data_mode, int ntaps,
                const double* crow_host, const double* ccol_host, const void* edge, int nl, int nr, int nt, int nb,
