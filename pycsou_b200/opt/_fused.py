@@ -253,7 +253,7 @@ def last_launch():
     keys = ('kernel', 'blocks', 'threads', 'smem', 'strips', 'strip_cols', 'n_fast', 'use_tma')
     d = dict(zip(keys, (int(v) for v in out)))
     d['kernel'] = {0: 'pds_tv_kernel', 1: 'pds_tv_ws_kernel', 2: 'pds_tv_persist_kernel',
-                   3: 'pds_tv_resident_kernel'}.get(d['kernel'], 'none')
+                   3: 'pds_tv_resident_kernel', 4: 'pds_tv_ws3_kernel'}.get(d['kernel'], 'none')
     return d
 
 
