@@ -89,7 +89,7 @@ def test_c3_fp32_4096_warp_specialised_uneven_split(c3_oracle):
     est, _, _ = s.iterate()
     L = m['last_launch']()
     # the benchmarked fp32 launch: warp-specialised kernel, one wave, %smid companion search + uneven long/short split
-    assert L['kernel'] == 'pds_tv_ws_kernel' and L['use_tma'] == 1 and L['threads'] == 384
+    assert L['kernel'] == 'pds_tv_ws3_kernel' and L['use_tma'] == 1 and L['threads'] == 512
     assert L['n_fast'] >= 0 and 148 < L['blocks'] <= 296
     x = est['primal_variable'].astype(np.float64)
     fo, fg = c['objective'](c['x']), c['objective'](x)
@@ -183,7 +183,7 @@ def test_one_wave_uneven_split_geometry_on_a_small_image(dtype, nsm, monkeypatch
         _lib.call_plain('pcs_set_num_sms', prev)
     assert L['kernel'] == L0['kernel'] and L['blocks'] != L0['blocks'] and L['blocks'] <= 2 * nsm
     if dtype == 'float32':
-        assert L['kernel'] == 'pds_tv_ws_kernel'
+        assert L['kernel'] == 'pds_tv_ws3_kernel'
         if L['blocks'] > nsm:
             assert L['n_fast'] >= 0                       # uneven split + companion search were exercised
     assert np.array_equal(est['primal_variable'], base['primal_variable'])
@@ -255,3 +255,21 @@ def test_on_chip_resident_kernel_many_updates_in_chunks(monkeypatch):
     assert np.array_equal(est['primal_variable'], ref['primal_variable'])
     assert np.array_equal(est['dual_variable'], ref['dual_variable'])
     assert np.allclose(dest.to_numpy(dtype=float), dref.to_numpy(dtype=float), rtol=2e-5, atol=0, equal_nan=True)
+
+
+@pytest.mark.parametrize('shape', [(4096, 4096), (300, 600), (72, 256), (40, 264)])
+def test_three_role_fp32_kernel_is_bit_identical_to_the_two_role_one(shape, monkeypatch):
+    """pds_tv_ws3_kernel (row-pass, column-pass and pointwise warps as three roles, ring with a spare box, mbarrier
+    hand-over of ring boxes, setmaxnreg) against pds_tv_ws_kernel: identical iterates, full size and edge-strip shapes."""
+    from tests.test_gpu_fused import _problem, _run
+    m = _mods()
+    kw = _problem(shape, 'sep', 'nonneg', 'l21', 'float32')
+    k = 4 if shape[0] > 1000 else 9
+    monkeypatch.setenv('PCS_PDS_WS3', '0')
+    _, ref, _ = _run(kw, k, True)
+    assert m['last_launch']()['kernel'] == 'pds_tv_ws_kernel'
+    monkeypatch.setenv('PCS_PDS_WS3', '1')
+    _, est, _ = _run(kw, k, True)
+    assert m['last_launch']()['kernel'] == 'pds_tv_ws3_kernel'
+    assert np.array_equal(est['primal_variable'], ref['primal_variable'])
+    assert np.array_equal(est['dual_variable'], ref['dual_variable'])
