@@ -861,8 +861,18 @@ def c5_arm(args, rank, local_rank, world, emit=True):
     return line
 
 
+def _json_only_stdout():
+    """The contract is ONE JSON line on stdout.  Native libraries write there too (NCCL prints its version banner on
+    stdout at N > 1): point file descriptor 1 at stderr for the whole run and keep the real stdout for `print` only."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, 'w', buffering=1)
+
+
 def main():
     args = parse_args()
+    _json_only_stdout()
     rank = int(os.environ.get('RANK', '0'))
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
