@@ -46,8 +46,8 @@ LAMBDA = 0.02
 NOISE = 0.02
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the fused kernel, from the committed `ncu --set full`
 # captures named in NCU_SOURCE (bench.py cannot run under ncu itself)
-NCU_DRAM_BYTES = {('f32', 4096, 'sep'): 441034240, ('f64', 4096, 'sep'): 962170368}
-NCU_SOURCE = 'profiles/r01_ncu_pds_f32_v14_ws.txt, r01_ncu_pds_f64_v13.txt (ncu --set full, one launch)'
+NCU_DRAM_BYTES = {('f32', 4096, 'sep'): 445905152, ('f64', 4096, 'sep'): 957700864}
+NCU_SOURCE = 'profiles/r02_ncu_pds_f32_ws3.txt, r02_ncu_pds_f64.txt (ncu --set full, one launch: dram read + write bytes)'
 
 
 def parse_args():

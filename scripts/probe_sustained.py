@@ -13,6 +13,9 @@ import bench
 dtype = sys.argv[1] if len(sys.argv) > 1 else 'f64'
 chunks = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 tdt = torch.float32 if dtype == 'f32' else torch.float64
+if os.environ.get('PCS_PROBE_NUM_SMS'):          # geometry built for fewer SMs than the device has (pcs_set_num_sms)
+    from pycsou_b200 import _lib
+    _lib.call_plain('pcs_set_num_sms', int(os.environ['PCS_PROBE_NUM_SMS']))
 psf, y64 = bench.make_problem(4096, 'sep', 0)
 y = torch.from_numpy(y64.astype(np.float32 if dtype == 'f32' else np.float64)).cuda()
 s = bench.make_solver(y, psf, 4096, tdt, 10, 'torch')
@@ -40,6 +43,8 @@ t1 = time.perf_counter() - t_start
 time.sleep(0.3)
 proc.terminate()
 us = [10 * evs[c].elapsed_time(evs[c + 1]) for c in range(chunks)]
+from pycsou_b200.opt._fused import last_launch
+print(last_launch())
 print(f'[{dtype}] us/update per chunk of 100: ' + ' '.join(f'{u:.1f}' for u in us))
 print(f'[{dtype}] load from t={t0:.2f}s to t={t1:.2f}s; nvidia-smi (t, sm MHz, mem MHz, W, C, power_cap, hw_slow, sw_thermal):')
 for t, ln in rows[::4]:
