@@ -339,7 +339,16 @@ class PrimalDualSplitting(_DeviceLoop, GenericIterativeAlgorithm):
         if (plan is None or self._slab is not None or not hasattr(plan, 'run_many') or getattr(plan, 'data_mode', 3) == 3
                 or os.environ.get('PCS_PDS_BATCH', '1') == '0'):        # debug switch: one library call per update
             return None
-        return plan.run_many(state[0], state[1], n, self._diag_dev[it:it + n])
+        ev = getattr(self, '_kernel_events', None)         # bench.py: CUDA events around the update kernels of the solve
+        if ev is None:
+            return plan.run_many(state[0], state[1], n, self._diag_dev[it:it + n])
+        import torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = plan.run_many(state[0], state[1], n, self._diag_dev[it:it + n])
+        e1.record()
+        ev.append((e0, e1, int(n)))
+        return out
 
     def _make_plan(self):
         if self._slab is not None:
