@@ -65,6 +65,148 @@ template <typename R> struct CpsTvArgs {
     double* partials; unsigned int* ticket; double* diag_out;
 };
 
+// ---- row-marching form of the TV step (the default; the tile kernel below stays for PCS_CPS_TV_TILE=1) -------------------
+// The tile kernel reads w0 and w1 three times per pixel (twice for Grad^T w, once for the dual update), stages v through
+// shared memory with two block barriers per tile and computes point indices by division: 65 us for 268 MB at 2048^2
+// complex64.  Here a thread owns NC = 16 / sizeof(complex) adjacent columns and MARCHES down a segment of rows: x, g, w0,
+// w1 of a row are loaded once (16-byte coalesced loads, the next row's in flight while this one is worked on), w0 of the
+// row above and v of the row above stay in registers, the left neighbour's w1 and the right neighbour's v come from the
+// adjacent lanes by warp shuffles.  A warp covers 32 NC columns and owns 31 NC of them: its last lane only computes v
+// (needed as "right neighbour" by lane 30) -- no shared memory, no block barrier.  Per pixel the operations are those of
+// the tile kernel, in the same order.
+constexpr int CPM_NT = 128;                 // threads per block (4 warps: 124 NC owned columns)
+#ifndef CPM_MINB
+#define CPM_MINB 6
+#endif
+template <typename R, int NC> struct CpmRow { typename Cx<R>::type x[NC], g[NC], w0[NC], w1[NC]; };
+
+template <typename R, int NC>
+__device__ __forceinline__ void cpm_load_row(CpmRow<R, NC>& r, const CpsTvArgs<R>& A, int gi, int gj0, bool colok, int64_t N) {
+    typedef typename Cx<R>::type V;
+    const V zero = cmake<V, R>(R(0), R(0));
+    if (colok && gi < A.H) {
+        const int64_t idx = (int64_t)gi * A.W + gj0;
+        if (NC == 2) {
+            const float4 a = *reinterpret_cast<const float4*>(A.x + idx), b = *reinterpret_cast<const float4*>(A.g + idx);
+            const float4 c = *reinterpret_cast<const float4*>(A.w + idx), d = *reinterpret_cast<const float4*>(A.w + N + idx);
+            r.x[0] = cmake<V, R>((R)a.x, (R)a.y); r.x[NC - 1] = cmake<V, R>((R)a.z, (R)a.w);
+            r.g[0] = cmake<V, R>((R)b.x, (R)b.y); r.g[NC - 1] = cmake<V, R>((R)b.z, (R)b.w);
+            r.w0[0] = cmake<V, R>((R)c.x, (R)c.y); r.w0[NC - 1] = cmake<V, R>((R)c.z, (R)c.w);
+            r.w1[0] = cmake<V, R>((R)d.x, (R)d.y); r.w1[NC - 1] = cmake<V, R>((R)d.z, (R)d.w);
+        } else {
+            r.x[0] = A.x[idx]; r.g[0] = A.g[idx]; r.w0[0] = A.w[idx]; r.w1[0] = A.w[N + idx];
+        }
+    } else {
+#pragma unroll
+        for (int e = 0; e < NC; ++e) r.x[e] = r.g[e] = r.w0[e] = r.w1[e] = zero;
+    }
+}
+
+template <typename R>
+__global__ void __launch_bounds__(CPM_NT, CPM_MINB) cps_tv_march_kernel(const CpsTvArgs<R> A, int seg_rows) {
+    typedef typename Cx<R>::type V;
+    constexpr int NC = 16 / (int)sizeof(V);
+    __shared__ double red[4 * (CPM_NT / 32)];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int H = A.H, W = A.W;
+    const int64_t N = (int64_t)H * W;
+    const V zero = cmake<V, R>(R(0), R(0));
+    // columns: warp `gw` of the grid row covers [31 NC gw, + 32 NC); lane 31 is the redundant one
+    const int gw = (int)blockIdx.x * (CPM_NT / 32) + warp;
+    const int gj0 = gw * 31 * NC + lane * NC;
+    const bool colok = gj0 < W;                         // (W is a multiple of NC: all NC columns or none)
+    const bool owner = colok && lane < 31;
+    const int i0 = (int)blockIdx.y * seg_rows, i1 = min(H, i0 + seg_rows);
+    double s_dx = 0.0, s_x = 0.0, s_dw = 0.0, s_w = 0.0;
+    if (i0 < i1) {
+        V w0_up[NC], a0p[NC], a1p[NC], v_prev[NC];      // row i - 1: w0 (for Grad^T w of row i and the dual update), w1, v
+#pragma unroll
+        for (int e = 0; e < NC; ++e) {
+            w0_up[e] = (colok && i0 > 0) ? A.w[(int64_t)(i0 - 1) * W + gj0 + e] : zero;
+            a0p[e] = a1p[e] = v_prev[e] = zero;
+        }
+        CpmRow<R, NC> cur, nxt;
+        cpm_load_row<R, NC>(cur, A, i0, gj0, colok, N);
+        for (int i = i0; i <= i1; ++i) {                 // row i1 (if it exists): v only, for the dual update of row i1 - 1
+            if (i < i1) cpm_load_row<R, NC>(nxt, A, i + 1, gj0, colok && i + 1 <= i1, N);
+            // left neighbour's w1 (column gj0 - 1)
+            V w1l;
+            w1l.x = __shfl_up_sync(0xffffffffu, cur.w1[NC - 1].x, 1);
+            w1l.y = __shfl_up_sync(0xffffffffu, cur.w1[NC - 1].y, 1);
+            if (lane == 0) w1l = (colok && gj0 > 0 && i < H) ? A.w[N + (int64_t)i * W + gj0 - 1] : zero;
+            V v[NC];
+            const bool rowok = i < H;
+#pragma unroll
+            for (int e = 0; e < NC; ++e) {
+                const int gj = gj0 + e;
+                v[e] = zero;
+                if (colok && rowok) {
+                    const V x = cur.x[e], g = cscale(cur.g[e], A.gscale);
+                    const V w0c = (i < H - 1) ? cur.w0[e] : zero, w0u = (i > 0) ? w0_up[e] : zero;
+                    const V w1c = (gj < W - 1) ? cur.w1[e] : zero;
+                    const V w1lv = (gj > 0) ? (e == 0 ? w1l : cur.w1[e == 0 ? 0 : e - 1]) : zero;
+                    V a = cscale(csub(w0u, w0c), A.is0);
+                    a = caxpy(a, A.is1, csub(w1lv, w1c));
+                    const V xt = caxpy(x, -A.tau, cadd(g, a));
+                    v[e] = caxpy(cscale(x, R(-1)), R(2), xt);
+                    if (owner && i < i1) {
+                        const V xn = caxpy(cscale(x, A.omr), A.rho, xt);
+                        cur.x[e] = xn;                      // (kept for the vector store below)
+                        s_dx += cabs2(csub(xn, x));
+                        s_x += cabs2(x);
+                    }
+                }
+            }
+            if (owner && i < i1) {
+                const int64_t idx = (int64_t)i * W + gj0;
+                if (NC == 2) {
+                    *reinterpret_cast<float4*>(A.x_out + idx) = make_float4((float)cur.x[0].x, (float)cur.x[0].y, (float)cur.x[NC - 1].x, (float)cur.x[NC - 1].y);
+                    *reinterpret_cast<float4*>(A.v_out + idx) = make_float4((float)v[0].x, (float)v[0].y, (float)v[NC - 1].x, (float)v[NC - 1].y);
+                } else {
+                    A.x_out[idx] = cur.x[0];
+                    A.v_out[idx] = v[0];
+                }
+            }
+            // dual update of row i - 1: needs v of rows i - 1 (v_prev) and i (v), and v_prev one column to the right
+            V vr_last;
+            vr_last.x = __shfl_down_sync(0xffffffffu, v_prev[0].x, 1);
+            vr_last.y = __shfl_down_sync(0xffffffffu, v_prev[0].y, 1);
+            if (i > i0 && owner) {
+                const int gi = i - 1;
+                V n0[NC], n1[NC];
+#pragma unroll
+                for (int e = 0; e < NC; ++e) {
+                    const int gj = gj0 + e;
+                    const V vc = v_prev[e], vd = v[e], vr = (e == NC - 1) ? vr_last : v_prev[e == NC - 1 ? e : e + 1];
+                    const V d0 = gi < H - 1 ? cscale(csub(vd, vc), A.is0) : zero;
+                    const V d1 = gj < W - 1 ? cscale(csub(vr, vc), A.is1) : zero;
+                    const V q0 = caxpy(a0p[e], A.sigma, d0), q1 = caxpy(a1p[e], A.sigma, d1);
+                    const R ss = fma(q0.x, q0.x, fma(q0.y, q0.y, fma(q1.x, q1.x, fma(q1.y, q1.y, tiny<R>()))));
+                    R f = A.lam * rsq<R>(ss);
+                    f = f < R(1) ? f : R(1);
+                    n0[e] = caxpy(cscale(a0p[e], A.omr), A.rho * f, q0);
+                    n1[e] = caxpy(cscale(a1p[e], A.omr), A.rho * f, q1);
+                    s_dw += cabs2(csub(n0[e], a0p[e])) + cabs2(csub(n1[e], a1p[e]));
+                    s_w += cabs2(a0p[e]) + cabs2(a1p[e]);
+                }
+                const int64_t idx = (int64_t)gi * W + gj0;
+                if (NC == 2) {
+                    *reinterpret_cast<float4*>(A.w_out + idx) = make_float4((float)n0[0].x, (float)n0[0].y, (float)n0[NC - 1].x, (float)n0[NC - 1].y);
+                    *reinterpret_cast<float4*>(A.w_out + N + idx) = make_float4((float)n1[0].x, (float)n1[0].y, (float)n1[NC - 1].x, (float)n1[NC - 1].y);
+                } else {
+                    A.w_out[idx] = n0[0];
+                    A.w_out[N + idx] = n1[0];
+                }
+            }
+#pragma unroll
+            for (int e = 0; e < NC; ++e) { w0_up[e] = cur.w0[e]; a0p[e] = cur.w0[e]; a1p[e] = cur.w1[e]; v_prev[e] = v[e]; }
+            cur = nxt;
+        }
+    }
+    double v4[4] = {s_dx, s_x, s_dw, s_w};
+    grid_sum_finish<4, CPM_NT>(v4, A.partials, A.ticket, A.diag_out, red);
+}
+
 template <typename R>
 __global__ void __launch_bounds__(CPS_NT) cps_tv_kernel(const CpsTvArgs<R> A) {
     typedef typename Cx<R>::type V;
@@ -348,6 +490,33 @@ int cps_tv_impl(void* x_out, void* w_out, void* v_out, const void* x, const void
     A.partials = (double*)workspace;
     A.ticket = (unsigned int*)((double*)workspace + 4 * (size_t)CPS_MAX_BLOCKS);
     A.diag_out = diag_out;
+    {
+        // row-marching kernel: needs 16-byte aligned rows and planes (PCS_CPS_TV_TILE=1 keeps the tile kernel)
+        constexpr int NC = 16 / (int)sizeof(V);
+        static const bool tile_only = [] { const char* e = getenv("PCS_CPS_TV_TILE"); return e && atoi(e) != 0; }();
+        bool ok = !tile_only && W % NC == 0 && ((H * W) % NC) == 0;
+        for (const void* q : {(const void*)x_out, (const void*)w_out, (const void*)v_out, x, w, g}) ok = ok && ((uintptr_t)q % 16) == 0;
+        if (ok) {
+            const int cols_per_block = (CPM_NT / 32) * 31 * NC;
+            const int gx = (int)((W + cols_per_block - 1) / cols_per_block);
+            // exactly ONE wave of resident blocks (a second, partial wave cost 1.3x), segments of at least 16 rows (a
+            // segment re-reads one row of w0 and recomputes one row of v)
+            int per_sm = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cps_tv_march_kernel<R>, CPM_NT, 0) != cudaSuccess || per_sm < 1) {
+                (void)cudaGetLastError();
+                per_sm = 4;
+            }
+            int64_t nseg = ((int64_t)per_sm * num_sms()) / gx;
+            if (nseg < 1) nseg = 1;
+            int64_t seg_rows = (H + nseg - 1) / nseg;
+            if (seg_rows < 16) seg_rows = 16;
+            nseg = (H + seg_rows - 1) / seg_rows;
+            if ((int64_t)gx * nseg <= CPS_MAX_BLOCKS) {
+                cps_tv_march_kernel<R><<<dim3((unsigned)gx, (unsigned)nseg), CPM_NT, 0, s>>>(A, (int)seg_rows);
+                return check_launch(what);
+            }
+        }
+    }
     constexpr int TW = TileW<R>::value;
     const int64_t ntiles = ((H + CPS_TH - 1) / CPS_TH) * ((W + TW - 1) / TW);
     // every tile its own block while the partial-sum slots last (6 blocks of 34 KB fit per SM), else a grid-stride loop
