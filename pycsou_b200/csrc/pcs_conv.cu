@@ -527,13 +527,21 @@ static int conv2d_sep_stream_launch(T* out, const T* x, const T* hcol, const T* 
     using G = CsGeo<T, K>;
     const int ca = (sgn > 0) ? off0 : K - 1 - off0, cb = (sgn > 0) ? off1 : K - 1 - off1;
     const int nstrips = (int)((W + CS_TC - 1) / CS_TC);
-    // ~4 blocks per SM; segments of at least 64 rows (the ring fill costs K - 1 extra rows per segment)
-    int nseg = (4 * num_sms() + nstrips - 1) / nstrips;
+    // exactly ONE wave of resident blocks (a few blocks left over for a second wave nearly double the time); segments of at
+    // least 64 rows (the ring fill costs K - 1 extra rows per segment)
+    cudaFuncSetAttribute(conv2d_sep_stream_kernel<T, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, conv2d_sep_stream_kernel<T, K>, CS_NT, G::SMEM) != cudaSuccess ||
+        per_sm < 1) {
+        (void)cudaGetLastError();
+        per_sm = 2;
+    }
+    int nseg = (per_sm * num_sms()) / nstrips;
+    if (nseg < 1) nseg = 1;
     int seg_rows = (int)((H + nseg - 1) / nseg);
     seg_rows = (seg_rows + CS_BR - 1) / CS_BR * CS_BR;
     if (seg_rows < 64) seg_rows = 64;
     nseg = (int)((H + seg_rows - 1) / seg_rows);
-    cudaFuncSetAttribute(conv2d_sep_stream_kernel<T, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
     conv2d_sep_stream_kernel<T, K><<<dim3((unsigned)nstrips, (unsigned)nseg), CS_NT, G::SMEM, s>>>(
         out, x, hcol, hrow, sgn, ca, cb, sub, (int)H, (int)W, seg_rows);
     return check_launch(what);
