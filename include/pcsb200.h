@@ -189,7 +189,8 @@ int pcs_mask_to_indices_static(const void* mask_u8, int64_t n, void* total_out_i
  *   workspace: pcs_pds_tv_workspace_bytes() bytes, zero-initialised once. */
 int64_t pcs_pds_tv_workspace_bytes(void);
 /* What the last pcs_pds_tv_step / _run / _step_slab call of the calling host thread launched (HOST int64[8]):
- * {kernel (0 single-role, 1 warp-specialised, 2 persistent multi-update), blocks, threads per block, dynamic shared memory, strips,
+ * {kernel (0 single-role, 1 warp-specialised with two roles, 2 persistent multi-update, 3 on-chip resident, 4 warp-specialised
+ *  with three roles), blocks, threads per block, dynamic shared memory, strips,
  *  output columns per strip, long segments of the uneven one-wave split (-1: even split), TMA staging used}.
  * Diagnostic only: the parity tests assert that the benchmarked kernel and geometry are the ones under test. */
 int pcs_pds_tv_last_launch(int64_t* out8_host);
