@@ -16,6 +16,12 @@
 // division are correctly rounded on both sides), so the number of updates is the reference's.
 #include "pcs_common.cuh"
 #include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <cooperative_groups.h>
+
+namespace cg = cooperative_groups;
 
 using namespace pcs;
 
@@ -40,6 +46,32 @@ template <typename T> struct ApgdArgs {
     long long it0, max_iter, min_iter;
     double* diag;         // rows of 4 doubles: ||x'-x||^2, ||x||^2, 0, 0 (row index = update index - it0)
     long long* n_iter;    // [0]: update index after the loop (the reference's self.iter); [1]: t as raw double bits
+};
+
+// The reference's stop test, `metric > threshold` with metric = sqrt(s_d) / sqrt(s_x) (inf when s_x = 0; opt/proxalgs.py:607-622),
+// decided without the two square roots and the division whenever the answer cannot depend on their rounding: the computed
+// metric is within 4 ulp of sqrt(s_d / s_x), so s_d > thr^2 (1 + 1e-12) s_x means `above` and s_d < thr^2 (1 - 1e-12) s_x
+// means `not above`; anything closer, non-finite or near the ends of the exponent range takes the reference's formula.
+struct StopTest {
+    double thr, lo, hi;
+    bool fast;
+    __device__ explicit StopTest(double threshold) : thr(threshold) {
+        const double t2 = threshold * threshold;
+        fast = t2 > 1e-290 && t2 < 1e290;
+        lo = t2 * (1.0 - 1e-12);
+        hi = t2 * (1.0 + 1e-12);
+    }
+    __device__ __forceinline__ bool above(double s_d, double s_x) const {
+        if (fast) {
+            const double ph = hi * s_x, pl = lo * s_x;
+            if (pl > 1e-290 && ph < 1e290) {
+                if (s_d > ph) return true;
+                if (s_d < pl) return false;
+            }
+        }
+        const double metric = s_x == 0.0 ? INFINITY : sqrt(s_d) / sqrt(s_x);
+        return metric > thr;
+    }
 };
 
 // deterministic block sum of two doubles (fixed tree), result broadcast to every thread
@@ -100,9 +132,11 @@ __global__ void __launch_bounds__(NT, 1) apgd_run_kernel(const ApgdArgs<T> A) {
     __syncthreads();
 
     const T tau = A.tau;
-    double t_old = A.t0, metric = INFINITY;
+    const StopTest stop(A.threshold);
+    double t_old = A.t0;
+    bool above = INFINITY > A.threshold;                         // metric starts at inf
     long long it = A.it0;
-    while ((it <= A.max_iter && metric > A.threshold) || it <= A.min_iter) {      // core/solver.py:65-66
+    while ((it <= A.max_iter && above) || it <= A.min_iter) {      // core/solver.py:65-66
         // residual r = h * x - y : (h * x)[i0 + e] = sum_k h[k] x[i0 + e + off - k]
         if (active) {
             T acc[EPT];
@@ -175,7 +209,7 @@ __global__ void __launch_bounds__(NT, 1) apgd_run_kernel(const ApgdArgs<T> A) {
             double* row = A.diag + 4 * (it - A.it0);
             row[0] = s_d; row[1] = s_x; row[2] = 0.0; row[3] = 0.0;
         }
-        metric = s_x == 0.0 ? INFINITY : sqrt(s_d) / sqrt(s_x);  // opt/proxalgs.py:607-622 (np.linalg.norm ratio)
+        above = stop.above(s_d, s_x);                            // opt/proxalgs.py:607-622 (np.linalg.norm ratio)
         t_old = t;
         ++it;
     }
@@ -190,6 +224,303 @@ __global__ void __launch_bounds__(NT, 1) apgd_run_kernel(const ApgdArgs<T> A) {
         A.n_iter[0] = it;
         A.n_iter[1] = __double_as_longlong(t_old);
     }
+}
+
+// ---- the same solve on a CLUSTER of thread blocks --------------------------------------------------------------------------
+// One SM bounds the single-block kernel: at N = 4096 with a 65-tap filter an update is 532 k FP64 multiply-adds = 4.4 us of one
+// SM's FP64 pipe (11.5 us measured).  Here a thread-block cluster (16 blocks, 8 if the device cannot place 16) shares the
+// vector: block c owns M = NT EPT consecutive elements and keeps them (and the residual) in ITS shared memory with a halo
+// on either side.  The thread that computes an element near the edge of the segment also stores it into the neighbour's
+// halo with st.async -- a store through distributed shared memory that counts its bytes on an mbarrier in the RECEIVING
+// block -- so a block waits only for its own two neighbours and only for the bytes it is about to read.  (A cluster
+// barrier with release semantics costs a MEMBAR.ALL.GPU per arrival: 0.9-1.5 k cycles per barrier, two per update, were
+// half the time of the first version of this kernel.)  No signal is needed in the other direction: a block can only be
+// sent new halo values by a neighbour that has received the values computed FROM the old ones, and the threads that read
+// a halo are among those that send the edge values (EXW below covers the filter's reach).
+// The stop test stays live: each warp's two partial sums go by the same kind of store into a slot of EVERY block (two
+// sets of slots, alternating, because a fast block may send the next update's sums while a slow one still reads), and
+// all blocks add the slots in the same order -- the same decision everywhere, no global memory, no host.  Per element
+// the operations are those of the single-block kernel, in the same order; only the two sums are added in another order.
+__device__ __forceinline__ uint32_t apc_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t apc_mapa(uint32_t addr, int rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void apc_st_async(uint32_t raddr, double v, uint32_t rbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(raddr),
+                 "l"(__double_as_longlong(v)), "r"(rbar) : "memory");
+}
+__device__ __forceinline__ void apc_st_async(uint32_t raddr, float v, uint32_t rbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(raddr),
+                 "r"(__float_as_uint(v)), "r"(rbar) : "memory");
+}
+__device__ __forceinline__ void apc_mbar_init(uint32_t bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void apc_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void apc_mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "APC_WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra APC_DONE_%=;\n\t"
+        "bra APC_WAIT_%=;\n\t"
+        "APC_DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+constexpr int APC_MAXCL = 16;
+template <typename T, int EPT, int APC_NT>
+__global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<T> A) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    cg::cluster_group cluster = cg::this_cluster();
+    const int rank = (int)cluster.block_rank(), CL = (int)cluster.num_blocks();
+    constexpr int C = APGD_C, M = APC_NT * EPT, NW = APC_NT / 32;
+    const int n = A.n, off = A.offset;
+    const int nhp = (A.nh + C - 1) / C * C;
+    const int EXW = nhp + C;                                   // elements stored into a neighbour's halo (<= M, checked by the host)
+    constexpr int HP = APGD_PAD;
+    constexpr int LEN = M + 2 * HP;
+    T* const bx = reinterpret_cast<T*>(smem);                  // iterate: halo | own | halo
+    T* const br = bx + LEN;                                    // residual, same layout
+    T* const sh = br + LEN;                                    // taps, zero padded to nhp
+    double* const parts = reinterpret_cast<double*>(smem + ((size_t)(2 * LEN + APGD_MAX_TAPS) * sizeof(T) + 15) / 16 * 16);   // [2][CL][warps][2]
+    unsigned long long* const bars = reinterpret_cast<unsigned long long*>(parts + 2 * APC_MAXCL * NW * 2);   // x halo, r halo, sums[2]
+    T* const sx = bx + HP;                                     // own element j of this block at sx[j]
+    T* const sr = br + HP;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int j0 = tid * EPT, g0 = rank * M + j0;              // local / global index of the thread's first element
+    const uint32_t bar_x = apc_smem_u32(bars), bar_r = bar_x + 8, bar_p = bar_x + 16;
+    const bool has_l = rank > 0, has_r = rank + 1 < CL;
+
+    for (int i = tid; i < 2 * LEN + APGD_MAX_TAPS; i += APC_NT) reinterpret_cast<T*>(smem)[i] = T(0);
+    if (tid == 0) {
+        for (int b = 0; b < 4; ++b) apc_mbar_init(bar_x + 8 * b, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    cluster.sync();                                            // nobody stores into memory that is still being cleared; barriers exist
+    T xa[EPT], pa[EPT], ya[EPT];
+#pragma unroll
+    for (int e = 0; e < EPT; ++e) {
+        const int i = g0 + e;
+        xa[e] = i < n ? A.x[i] : T(0);
+        pa[e] = i < n ? A.aux[i] : T(0);
+        ya[e] = i < n ? A.y[i] : T(0);
+        sx[j0 + e] = xa[e];
+    }
+    for (int k = tid; k < A.nh; k += APC_NT) sh[k] = A.h[k];
+    // Where this block's edge values go: the same offsets in the neighbours' copies of the two arrays, and their barriers.
+    const uint32_t lbx = has_l ? apc_mapa(apc_smem_u32(bx), rank - 1) : 0u, rbx = has_r ? apc_mapa(apc_smem_u32(bx), rank + 1) : 0u;
+    const uint32_t lbr = has_l ? apc_mapa(apc_smem_u32(br), rank - 1) : 0u, rbr = has_r ? apc_mapa(apc_smem_u32(br), rank + 1) : 0u;
+    const uint32_t lbar = has_l ? apc_mapa(bar_x, rank - 1) : 0u, rbar = has_r ? apc_mapa(bar_x, rank + 1) : 0u;   // (+8: their bar_r)
+    // local element j goes to the right halo of the block on the left when j < EXW, to the left halo of the block on the
+    // right when j >= M - EXW
+    auto push = [&](uint32_t left, uint32_t right, uint32_t bar_off, int j, T v) {
+        if (has_l && j < EXW) apc_st_async(left + (uint32_t)((HP + M + j) * sizeof(T)), v, lbar + bar_off);
+        if (has_r && j >= M - EXW) apc_st_async(right + (uint32_t)((HP - EXW + (j - (M - EXW))) * sizeof(T)), v, rbar + bar_off);
+    };
+    const uint32_t hbytes = (uint32_t)(((has_l ? EXW : 0) + (has_r ? EXW : 0)) * sizeof(T));
+    const uint32_t pbytes = (uint32_t)(CL * NW * 2 * sizeof(double));
+    const uint32_t my_parts = lane < CL ? apc_mapa(apc_smem_u32(parts), lane) : 0u, my_pbar = lane < CL ? apc_mapa(bar_p, lane) : 0u;
+    if (tid == 0) apc_mbar_expect_tx(bar_x, hbytes);
+#pragma unroll
+    for (int e = 0; e < EPT; ++e) push(lbx, rbx, 0u, j0 + e, xa[e]);
+    __syncthreads();                                           // own part of sx and the taps are complete
+    uint32_t ph_x = 0, ph_r = 0, ph_p = 0;                     // phase parities (ph_p: bit b for set b of the sums)
+    unsigned kk = 0;                                           // updates done in this launch
+
+#ifdef APC_PHASE_TIMING
+    long long ph[6] = {0, 0, 0, 0, 0, 0}, tk = clock64();
+#define APC_TICK(i) { const long long now_ = clock64(); ph[i] += now_ - tk; tk = now_; }
+#else
+#define APC_TICK(i)
+#endif
+    const T tau = A.tau;
+    const StopTest stop(A.threshold);
+    double t_old = A.t0;
+    bool above = INFINITY > A.threshold;                         // metric starts at inf
+    long long it = A.it0;
+    while ((it <= A.max_iter && above) || it <= A.min_iter) {
+        const unsigned set = kk & 1u;
+        if (tid == 0) {
+            apc_mbar_expect_tx(bar_r, hbytes);
+            apc_mbar_expect_tx(bar_p + 8 * set, pbytes);
+        }
+        apc_mbar_wait(bar_x, ph_x);                              // the neighbours' edge values of x are in the halos
+        ph_x ^= 1u;
+        {   // residual r = h * x - y on the own segment
+            T acc[EPT];
+#pragma unroll
+            for (int e = 0; e < EPT; ++e) acc[e] = T(0);
+            const T* px = sx + j0 + off;
+#pragma unroll 3
+            for (int K = 0; K < nhp; K += C) {
+                T hk[C], wv[EPT + C - 1];
+#pragma unroll
+                for (int c = 0; c < C; ++c) hk[c] = sh[K + c];
+#pragma unroll
+                for (int m = 0; m < EPT + C - 1; ++m) wv[m] = px[m - K - (C - 1)];
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+#pragma unroll
+                    for (int e = 0; e < EPT; ++e) acc[e] = fma(hk[c], wv[e - c + C - 1], acc[e]);
+            }
+#pragma unroll
+            for (int e = 0; e < EPT; ++e) {
+                const T rv = (g0 + e < n) ? acc[e] - ya[e] : T(0);
+                sr[j0 + e] = rv;
+                push(lbr, rbr, 8u, j0 + e, rv);
+            }
+        }
+        APC_TICK(0)
+        __syncthreads();                                         // own part of sr complete (and every thread is past the wait on bar_x)
+        if (tid == 0) apc_mbar_expect_tx(bar_x, hbytes);         // next update's x halos
+        double t, a;
+        if (A.accel == ACC_BT) t = (1.0 + sqrt(1.0 + 4.0 * t_old * t_old)) / 2.0;
+        else if (A.accel == ACC_CD) t = ((double)it + A.d) / A.d;
+        else { t = 1.0; t_old = 1.0; }
+        a = (t_old - 1.0) / t;
+        const T ta = (T)a, t1a = (T)(1.0 + a);
+        apc_mbar_wait(bar_r, ph_r);                              // the neighbours' edge values of r are in the halos
+        ph_r ^= 1u;
+        APC_TICK(1)
+        double s_d = 0.0, s_x = 0.0;
+        {
+            T g[EPT];
+#pragma unroll
+            for (int e = 0; e < EPT; ++e) g[e] = T(0);
+            const T* pr = sr + j0 - off;
+#pragma unroll 3
+            for (int K = 0; K < nhp; K += C) {
+                T hk[C], wv[EPT + C - 1];
+#pragma unroll
+                for (int c = 0; c < C; ++c) hk[c] = sh[K + c];
+#pragma unroll
+                for (int m = 0; m < EPT + C - 1; ++m) wv[m] = pr[K + m];
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+#pragma unroll
+                    for (int e = 0; e < EPT; ++e) g[e] = fma(hk[c], wv[e + c], g[e]);
+            }
+#pragma unroll
+            for (int e = 0; e < EPT; ++e) {
+                if (g0 + e < n) {
+                    const T v = xa[e] - mul_rn(tau, g[e]);
+                    T p;
+                    if (A.g_mode == AG_L1) p = prox_l1<T>(v, A.g_param);
+                    else if (A.g_mode == AG_NONNEG) p = v < T(0) ? T(0) : v;
+                    else p = v;
+                    const T xn = mul_rn(t1a, p) - mul_rn(ta, pa[e]);
+                    const double dd = (double)xn - (double)xa[e];
+                    s_d += dd * dd;
+                    s_x += (double)xa[e] * (double)xa[e];
+                    pa[e] = p;
+                    xa[e] = xn;
+                }
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < EPT; ++e) {
+            sx[j0 + e] = xa[e];
+            push(lbx, rbx, 0u, j0 + e, xa[e]);
+        }
+        APC_TICK(2)
+        s_d = warp_sum(s_d);                                     // each WARP's partial sums go into slot (rank, warp) of every block
+        s_x = warp_sum(s_x);
+        if (lane < CL) {
+            const uint32_t slot = (uint32_t)(((set * CL + rank) * NW + warp) * 2 * sizeof(double));
+            apc_st_async(my_parts + slot, s_d, my_pbar + 8 * set);
+            apc_st_async(my_parts + slot + 8, s_x, my_pbar + 8 * set);
+        }
+        APC_TICK(3)
+        __syncthreads();                                         // own part of sx complete; every thread is past the wait on bar_r
+        apc_mbar_wait(bar_p + 8 * set, (ph_p >> set) & 1u);      // all blocks' sums of this update
+        ph_p ^= 1u << set;
+        APC_TICK(4)
+        s_d = 0.0; s_x = 0.0;
+        const double* pp = parts + (size_t)set * CL * NW * 2;
+        for (int c = lane; c < CL * NW; c += 32) { s_d += pp[2 * c]; s_x += pp[2 * c + 1]; }
+        s_d = warp_sum(s_d);                                     // same slots, same order in every warp of every block
+        s_x = warp_sum(s_x);
+        if (rank == 0 && tid == 0) {
+            double* row = A.diag + 4 * (it - A.it0);
+            row[0] = s_d; row[1] = s_x; row[2] = 0.0; row[3] = 0.0;
+        }
+        above = stop.above(s_d, s_x);
+        t_old = t;
+        ++it;
+        ++kk;
+        APC_TICK(5)
+    }
+#ifdef APC_PHASE_TIMING
+    if (tid == 0 && (rank == 1 || rank == CL - 1))
+        printf("apgd cluster rank %d: %lld updates; cycles per update: residual %lld, wait r %lld, gradient+prox %lld, sums+push %lld, wait sums %lld, tail %lld\n",
+               rank, it - A.it0, ph[0] / (it - A.it0), ph[1] / (it - A.it0), ph[2] / (it - A.it0), ph[3] / (it - A.it0), ph[4] / (it - A.it0),
+               ph[5] / (it - A.it0));
+#endif
+#pragma unroll
+    for (int e = 0; e < EPT; ++e) {
+        if (g0 + e < n) {
+            A.x[g0 + e] = xa[e];
+            A.aux[g0 + e] = pa[e];
+        }
+    }
+    if (rank == 0 && tid == 0) {
+        A.n_iter[0] = it;
+        A.n_iter[1] = __double_as_longlong(t_old);
+    }
+    apc_mbar_wait(bar_x, ph_x);                                  // everything sent to this block has arrived ...
+    cluster.sync();                                              // ... and that holds for every block: nothing is in flight when one leaves
+}
+
+// Returns -1 when the cluster kernel cannot run this problem (the caller falls back to the single-block kernel).
+template <typename T, int EPT, int APC_NT> int apgd_cluster_launch(const ApgdArgs<T>& A, int CL, cudaStream_t s) {
+    constexpr int M = APC_NT * EPT;
+    const size_t smem = ((size_t)(2 * (M + 2 * APGD_PAD) + APGD_MAX_TAPS) * sizeof(T) + 15) / 16 * 16 + (2 * 2 * APC_MAXCL * (APC_NT / 32)) * sizeof(double) + 4 * sizeof(unsigned long long);
+    auto kern = apgd_cluster_kernel<T, EPT, APC_NT>;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
+        cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return -1;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)CL); cfg.blockDim = dim3(APC_NT); cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    int nclusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&nclusters, kern, &cfg) != cudaSuccess || nclusters < 1) {
+        (void)cudaGetLastError();
+        return -1;
+    }
+    if (cudaLaunchKernelEx(&cfg, kern, A) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return -1;
+    }
+    return check_launch("pcs_apgd_conv1d_run");
+}
+template <typename T> int apgd_cluster_try(const ApgdArgs<T>& A, cudaStream_t s) {
+    const char* env = getenv("PCS_APGD_CLUSTER");               // PCS_APGD_CLUSTER=0 keeps the single-block kernel (read per call)
+    if ((env && atoi(env) == 0) || A.n < 2048) return -1;
+    const char* envt = getenv("PCS_APGD_CLUSTER_NT");
+    const int want_nt = envt ? atoi(envt) : 0;
+    const int nhp = (A.nh + APGD_C - 1) / APGD_C * APGD_C, exw = nhp + APGD_C;
+    for (int CL : {16, 8}) {
+        const int per = (A.n + CL - 1) / CL;
+        for (int nt : {256, 128}) {
+            if (want_nt && nt != want_nt) continue;
+            const int ept = per <= nt ? 1 : (per <= 2 * nt ? 2 : (per <= 4 * nt ? 4 : 0));
+            if (ept == 0 || nt * ept < exw || (nt == 256 && ept == 4)) continue;
+            int rc;
+            if (nt == 256) rc = ept == 1 ? apgd_cluster_launch<T, 1, 256>(A, CL, s) : apgd_cluster_launch<T, 2, 256>(A, CL, s);
+            else rc = ept == 1 ? apgd_cluster_launch<T, 1, 128>(A, CL, s) : (ept == 2 ? apgd_cluster_launch<T, 2, 128>(A, CL, s)
+                                                                                      : apgd_cluster_launch<T, 4, 128>(A, CL, s));
+            if (rc != -1) return rc;
+        }
+    }
+    return -1;
 }
 
 template <typename T, int EPT, int NT> int apgd_launch(const ApgdArgs<T>& A, size_t smem, cudaStream_t s) {
@@ -213,6 +544,10 @@ int pcs_apgd_conv1d_run_impl(T* x, T* aux, const T* y, const T* h, int nh, int o
     A.x = x; A.aux = aux; A.y = y; A.h = h; A.nh = nh; A.offset = offset; A.n = (int)n; A.g_mode = g_mode;
     A.accel = accel; A.g_param = (T)g_param; A.tau = (T)tau; A.d = d; A.t0 = t0; A.threshold = threshold;
     A.it0 = it0; A.max_iter = max_iter; A.min_iter = min_iter; A.diag = diag; A.n_iter = n_iter;
+    {
+        const int rc = apgd_cluster_try<T>(A, s);              // a thread-block cluster shares the vector where it can
+        if (rc != -1) return rc;
+    }
     const size_t smem = ((size_t)(2 * (n + 2 * APGD_PAD) + APGD_MAX_TAPS) * sizeof(T) + 15) / 16 * 16 + 66 * sizeof(double);
     PCS_REQUIRE(smem <= 227 * 1024, "%s: problem does not fit in shared memory", what);
     // Up to 17 consecutive elements per thread (17 independent FMA chains, ~1.4 shared loads per 8 FMAs).  The count
