@@ -265,12 +265,48 @@ __device__ __forceinline__ void apc_mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "APC_WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
         "@p bra APC_DONE_%=;\n\t"
         "bra APC_WAIT_%=;\n\t"
         "APC_DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
 }
 constexpr int APC_MAXCL = 16;
+template <typename T> struct ApcPair;
+template <> struct ApcPair<double> { using type = double2; };
+template <> struct ApcPair<float> { using type = float2; };
+// One filter pass over a thread's EPT consecutive elements (EPT even, first element at an even index): for every group of C
+// taps the EPT + C - 1 samples under them are read as aligned PAIRS (LDS.128 for doubles: 4 wavefronts for 64 values, the
+// shared-memory bandwidth, where a 64-bit load at a stride of two doubles also costs 4) -- shared-memory wavefronts, not
+// the FP64 pipe, bound this kernel.  `win` points at the first sample of the window of the first group, minus SH (0 or 1)
+// so that it is pair-aligned; the window of group K starts K samples before it (DIR = -1, convolution) or after it
+// (DIR = +1, correlation); tap c of the group multiplies sample e + C - 1 - c (DIR = -1) or e + c (DIR = +1) of element e.
+template <typename T, int EPT, int SH, int DIR>
+__device__ __forceinline__ void apc_tap_pass(const T* win, const T* sh, int nhp, T (&acc)[EPT][APGD_C]) {
+    constexpr int C = APGD_C, NP = (EPT + C - 1 + SH + 1) / 2;
+    using P = typename ApcPair<T>::type;
+#pragma unroll 3
+    for (int K = 0; K < nhp; K += C) {
+        T hk[C], w[2 * NP];
+#pragma unroll
+        for (int c = 0; c < C; ++c) hk[c] = sh[K + c];
+        const P* q = reinterpret_cast<const P*>(win + DIR * K);
+#pragma unroll
+        for (int i = 0; i < NP; ++i) {
+            const P v = q[i];
+            w[2 * i] = v.x;
+            w[2 * i + 1] = v.y;
+        }
+#pragma unroll
+        for (int c = 0; c < C; ++c)
+#pragma unroll
+            for (int e = 0; e < EPT; ++e) acc[e][c] = fma(hk[c], w[SH + (DIR < 0 ? e - c + C - 1 : e + c)], acc[e][c]);
+    }
+}
+// The C running sums of an element (one per tap position within a group of C taps) are added in this fixed order.
+template <typename T> __device__ __forceinline__ T tap_tree(const T (&a)[APGD_C]) {
+    static_assert(APGD_C == 8, "tap_tree is written for groups of 8 taps");
+    return ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
+}
 template <typename T, int EPT, int APC_NT>
 __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<T> A) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -285,8 +321,8 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
     T* const bx = reinterpret_cast<T*>(smem);                  // iterate: halo | own | halo
     T* const br = bx + LEN;                                    // residual, same layout
     T* const sh = br + LEN;                                    // taps, zero padded to nhp
-    double* const parts = reinterpret_cast<double*>(smem + ((size_t)(2 * LEN + APGD_MAX_TAPS) * sizeof(T) + 15) / 16 * 16);   // [2][CL][warps][2]
-    unsigned long long* const bars = reinterpret_cast<unsigned long long*>(parts + 2 * APC_MAXCL * NW * 2);   // x halo, r halo, sums[2]
+    double* const parts = reinterpret_cast<double*>(smem + ((size_t)(2 * LEN + APGD_MAX_TAPS) * sizeof(T) + 15) / 16 * 16);   // [4][16][warps][2]
+    unsigned long long* const bars = reinterpret_cast<unsigned long long*>(parts + 4 * APC_MAXCL * NW * 2);   // x halo, r halo, sums[4]
     T* const sx = bx + HP;                                     // own element j of this block at sx[j]
     T* const sr = br + HP;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -295,8 +331,9 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
     const bool has_l = rank > 0, has_r = rank + 1 < CL;
 
     for (int i = tid; i < 2 * LEN + APGD_MAX_TAPS; i += APC_NT) reinterpret_cast<T*>(smem)[i] = T(0);
+    for (int i = tid; i < 4 * APC_MAXCL * NW * 2; i += APC_NT) parts[i] = 0.0;
     if (tid == 0) {
-        for (int b = 0; b < 4; ++b) apc_mbar_init(bar_x + 8 * b, 1);
+        for (int b = 0; b < 6; ++b) apc_mbar_init(bar_x + 8 * b, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     cluster.sync();                                            // nobody stores into memory that is still being cleared; barriers exist
@@ -328,10 +365,9 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
     for (int e = 0; e < EPT; ++e) push(lbx, rbx, 0u, j0 + e, xa[e]);
     __syncthreads();                                           // own part of sx and the taps are complete
     uint32_t ph_x = 0, ph_r = 0, ph_p = 0;                     // phase parities (ph_p: bit b for set b of the sums)
-    unsigned kk = 0;                                           // updates done in this launch
 
 #ifdef APC_PHASE_TIMING
-    long long ph[6] = {0, 0, 0, 0, 0, 0}, tk = clock64();
+    long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tk = clock64();
 #define APC_TICK(i) { const long long now_ = clock64(); ph[i] += now_ - tk; tk = now_; }
 #else
 #define APC_TICK(i)
@@ -339,42 +375,71 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
     const T tau = A.tau;
     const StopTest stop(A.threshold);
     double t_old = A.t0;
-    bool above = INFINITY > A.threshold;                         // metric starts at inf
     long long it = A.it0;
-    while ((it <= A.max_iter && above) || it <= A.min_iter) {
-        const unsigned set = kk & 1u;
+    bool pending = false;                                        // the sums of update it - 1 have not been looked at yet
+    // Adds the sums of update `upd` (set upd & 3) once they are all here, writes its row of diagnostics, returns the stop test.
+    auto settle = [&](long long upd) -> bool {
+        const unsigned set = (unsigned)(upd - A.it0) & 3u;
+        apc_mbar_wait(bar_p + 8 * set, (ph_p >> set) & 1u);
+        ph_p ^= 1u << set;
+        const double* pp = parts + (size_t)set * APC_MAXCL * NW * 2;
+        double s_d = 0.0, s_x = 0.0;
+#pragma unroll
+        for (int c = 0; c < APC_MAXCL * NW / 32; ++c) {          // (slots of absent blocks stay zero)
+            s_d += pp[2 * (lane + 32 * c)];
+            s_x += pp[2 * (lane + 32 * c) + 1];
+        }
+        s_d = warp_sum(s_d);                                     // same slots, same order in every warp of every block
+        s_x = warp_sum(s_x);
+        if (rank == 0 && tid == 0) {
+            double* row = A.diag + 4 * (upd - A.it0);
+            row[0] = s_d; row[1] = s_x; row[2] = 0.0; row[3] = 0.0;
+        }
+        return stop.above(s_d, s_x);
+    };
+    // core/solver.py:65-66: update `it` runs when (it <= max_iter and metric(it - 1) > threshold) or it <= min_iter, the metric
+    // before the first update being inf.  The sums behind metric(it - 1) come from all blocks, so waiting for them would put
+    // an all-to-all exchange on the path of every update; instead update `it` STARTS as soon as the neighbours' halos are in,
+    // on the assumption that the metric was above the threshold, and the sums of update it - 1 are looked at when update
+    // `it` is half done -- after its residual pass, while the neighbours' edge values of the residual are on their way; the
+    // sums arrived long before.  If they say stop, the update is dropped: the iterate has not been touched yet.  What the
+    // caller gets -- iterates, number of updates, diagnostics -- is what the reference's loop gives.
+    bool dropped = false;
+    bool go = (it <= A.max_iter && INFINITY > A.threshold) || it <= A.min_iter;
+    while (go) {
+        const unsigned set = (unsigned)(it - A.it0) & 3u;
         if (tid == 0) {
             apc_mbar_expect_tx(bar_r, hbytes);
             apc_mbar_expect_tx(bar_p + 8 * set, pbytes);
         }
         apc_mbar_wait(bar_x, ph_x);                              // the neighbours' edge values of x are in the halos
         ph_x ^= 1u;
-        {   // residual r = h * x - y on the own segment
-            T acc[EPT];
+        APC_TICK(3)
+        {   // residual r = h * x - y on the own segment; tap c of every group of C has its own running sum
+            T acc[EPT][C];
 #pragma unroll
-            for (int e = 0; e < EPT; ++e) acc[e] = T(0);
-            const T* px = sx + j0 + off;
-#pragma unroll 3
-            for (int K = 0; K < nhp; K += C) {
-                T hk[C], wv[EPT + C - 1];
+            for (int e = 0; e < EPT; ++e)
 #pragma unroll
-                for (int c = 0; c < C; ++c) hk[c] = sh[K + c];
-#pragma unroll
-                for (int m = 0; m < EPT + C - 1; ++m) wv[m] = px[m - K - (C - 1)];
-#pragma unroll
-                for (int c = 0; c < C; ++c)
-#pragma unroll
-                    for (int e = 0; e < EPT; ++e) acc[e] = fma(hk[c], wv[e - c + C - 1], acc[e]);
-            }
+                for (int c = 0; c < C; ++c) acc[e][c] = T(0);
+            // first sample of the first window: x[j0 + off - (C - 1)]; j0 is even, so its parity is that of off + 1
+            if (off & 1) apc_tap_pass<T, EPT, 0, -1>(sx + j0 + off - (C - 1), sh, nhp, acc);
+            else apc_tap_pass<T, EPT, 1, -1>(sx + j0 + off - (C - 1) - 1, sh, nhp, acc);
 #pragma unroll
             for (int e = 0; e < EPT; ++e) {
-                const T rv = (g0 + e < n) ? acc[e] - ya[e] : T(0);
+                const T s = tap_tree(acc[e]);
+                const T rv = (g0 + e < n) ? s - ya[e] : T(0);
                 sr[j0 + e] = rv;
                 push(lbr, rbr, 8u, j0 + e, rv);
             }
         }
         APC_TICK(0)
         __syncthreads();                                         // own part of sr complete (and every thread is past the wait on bar_x)
+        if (pending && !settle(it - 1) && it > A.min_iter) {     // the loop had ended before this update: drop it
+            dropped = true;
+            pending = false;
+            break;
+        }
+        APC_TICK(6)
         if (tid == 0) apc_mbar_expect_tx(bar_x, hbytes);         // next update's x halos
         double t, a;
         if (A.accel == ACC_BT) t = (1.0 + sqrt(1.0 + 4.0 * t_old * t_old)) / 2.0;
@@ -387,26 +452,17 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
         APC_TICK(1)
         double s_d = 0.0, s_x = 0.0;
         {
-            T g[EPT];
+            T g[EPT][C];
 #pragma unroll
-            for (int e = 0; e < EPT; ++e) g[e] = T(0);
-            const T* pr = sr + j0 - off;
-#pragma unroll 3
-            for (int K = 0; K < nhp; K += C) {
-                T hk[C], wv[EPT + C - 1];
+            for (int e = 0; e < EPT; ++e)
 #pragma unroll
-                for (int c = 0; c < C; ++c) hk[c] = sh[K + c];
-#pragma unroll
-                for (int m = 0; m < EPT + C - 1; ++m) wv[m] = pr[K + m];
-#pragma unroll
-                for (int c = 0; c < C; ++c)
-#pragma unroll
-                    for (int e = 0; e < EPT; ++e) g[e] = fma(hk[c], wv[e + c], g[e]);
-            }
+                for (int c = 0; c < C; ++c) g[e][c] = T(0);
+            if (off & 1) apc_tap_pass<T, EPT, 1, +1>(sr + j0 - off - 1, sh, nhp, g);
+            else apc_tap_pass<T, EPT, 0, +1>(sr + j0 - off, sh, nhp, g);
 #pragma unroll
             for (int e = 0; e < EPT; ++e) {
                 if (g0 + e < n) {
-                    const T v = xa[e] - mul_rn(tau, g[e]);
+                    const T v = xa[e] - mul_rn(tau, tap_tree(g[e]));
                     T p;
                     if (A.g_mode == AG_L1) p = prox_l1<T>(v, A.g_param);
                     else if (A.g_mode == AG_NONNEG) p = v < T(0) ? T(0) : v;
@@ -429,35 +485,24 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
         s_d = warp_sum(s_d);                                     // each WARP's partial sums go into slot (rank, warp) of every block
         s_x = warp_sum(s_x);
         if (lane < CL) {
-            const uint32_t slot = (uint32_t)(((set * CL + rank) * NW + warp) * 2 * sizeof(double));
+            const uint32_t slot = (uint32_t)(((set * APC_MAXCL + rank) * NW + warp) * 2 * sizeof(double));
             apc_st_async(my_parts + slot, s_d, my_pbar + 8 * set);
             apc_st_async(my_parts + slot + 8, s_x, my_pbar + 8 * set);
         }
-        APC_TICK(3)
-        __syncthreads();                                         // own part of sx complete; every thread is past the wait on bar_r
-        apc_mbar_wait(bar_p + 8 * set, (ph_p >> set) & 1u);      // all blocks' sums of this update
-        ph_p ^= 1u << set;
         APC_TICK(4)
-        s_d = 0.0; s_x = 0.0;
-        const double* pp = parts + (size_t)set * CL * NW * 2;
-        for (int c = lane; c < CL * NW; c += 32) { s_d += pp[2 * c]; s_x += pp[2 * c + 1]; }
-        s_d = warp_sum(s_d);                                     // same slots, same order in every warp of every block
-        s_x = warp_sum(s_x);
-        if (rank == 0 && tid == 0) {
-            double* row = A.diag + 4 * (it - A.it0);
-            row[0] = s_d; row[1] = s_x; row[2] = 0.0; row[3] = 0.0;
-        }
-        above = stop.above(s_d, s_x);
+        __syncthreads();                                         // own part of sx complete; every thread is past the wait on bar_r
+        pending = true;
         t_old = t;
         ++it;
-        ++kk;
+        go = it <= A.max_iter || it <= A.min_iter;               // (and the metric above the threshold: settled after the update)
         APC_TICK(5)
     }
+    if (pending) settle(it - 1);                                 // the last update's row of diagnostics
 #ifdef APC_PHASE_TIMING
     if (tid == 0 && (rank == 1 || rank == CL - 1))
-        printf("apgd cluster rank %d: %lld updates; cycles per update: residual %lld, wait r %lld, gradient+prox %lld, sums+push %lld, wait sums %lld, tail %lld\n",
+        printf("apgd cluster rank %d: %lld updates; cycles per update: residual %lld, wait r %lld, gradient+prox %lld, wait x %lld, sums+push %lld, tail %lld, sync+settle %lld\n",
                rank, it - A.it0, ph[0] / (it - A.it0), ph[1] / (it - A.it0), ph[2] / (it - A.it0), ph[3] / (it - A.it0), ph[4] / (it - A.it0),
-               ph[5] / (it - A.it0));
+               ph[5] / (it - A.it0), ph[6] / (it - A.it0));
 #endif
 #pragma unroll
     for (int e = 0; e < EPT; ++e) {
@@ -470,14 +515,14 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
         A.n_iter[0] = it;
         A.n_iter[1] = __double_as_longlong(t_old);
     }
-    apc_mbar_wait(bar_x, ph_x);                                  // everything sent to this block has arrived ...
+    apc_mbar_wait(dropped ? bar_r : bar_x, dropped ? ph_r : ph_x);   // everything sent to this block has arrived ...
     cluster.sync();                                              // ... and that holds for every block: nothing is in flight when one leaves
 }
 
 // Returns -1 when the cluster kernel cannot run this problem (the caller falls back to the single-block kernel).
 template <typename T, int EPT, int APC_NT> int apgd_cluster_launch(const ApgdArgs<T>& A, int CL, cudaStream_t s) {
     constexpr int M = APC_NT * EPT;
-    const size_t smem = ((size_t)(2 * (M + 2 * APGD_PAD) + APGD_MAX_TAPS) * sizeof(T) + 15) / 16 * 16 + (2 * 2 * APC_MAXCL * (APC_NT / 32)) * sizeof(double) + 4 * sizeof(unsigned long long);
+    const size_t smem = ((size_t)(2 * (M + 2 * APGD_PAD) + APGD_MAX_TAPS) * sizeof(T) + 15) / 16 * 16 + (4 * 2 * APC_MAXCL * (APC_NT / 32)) * sizeof(double) + 6 * sizeof(unsigned long long);
     auto kern = apgd_cluster_kernel<T, EPT, APC_NT>;
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
         cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
@@ -504,21 +549,13 @@ template <typename T, int EPT, int APC_NT> int apgd_cluster_launch(const ApgdArg
 template <typename T> int apgd_cluster_try(const ApgdArgs<T>& A, cudaStream_t s) {
     const char* env = getenv("PCS_APGD_CLUSTER");               // PCS_APGD_CLUSTER=0 keeps the single-block kernel (read per call)
     if ((env && atoi(env) == 0) || A.n < 2048) return -1;
-    const char* envt = getenv("PCS_APGD_CLUSTER_NT");
-    const int want_nt = envt ? atoi(envt) : 0;
     const int nhp = (A.nh + APGD_C - 1) / APGD_C * APGD_C, exw = nhp + APGD_C;
     for (int CL : {16, 8}) {
         const int per = (A.n + CL - 1) / CL;
-        for (int nt : {256, 128}) {
-            if (want_nt && nt != want_nt) continue;
-            const int ept = per <= nt ? 1 : (per <= 2 * nt ? 2 : (per <= 4 * nt ? 4 : 0));
-            if (ept == 0 || nt * ept < exw || (nt == 256 && ept == 4)) continue;
-            int rc;
-            if (nt == 256) rc = ept == 1 ? apgd_cluster_launch<T, 1, 256>(A, CL, s) : apgd_cluster_launch<T, 2, 256>(A, CL, s);
-            else rc = ept == 1 ? apgd_cluster_launch<T, 1, 128>(A, CL, s) : (ept == 2 ? apgd_cluster_launch<T, 2, 128>(A, CL, s)
-                                                                                      : apgd_cluster_launch<T, 4, 128>(A, CL, s));
-            if (rc != -1) return rc;
-        }
+        const int ept = per <= 2 * 128 ? 2 : (per <= 4 * 128 ? 4 : 0);      // elements per thread: even (pair-aligned windows)
+        if (ept == 0 || 128 * ept < exw) continue;
+        const int rc = ept == 2 ? apgd_cluster_launch<T, 2, 128>(A, CL, s) : apgd_cluster_launch<T, 4, 128>(A, CL, s);
+        if (rc != -1) return rc;
     }
     return -1;
 }

@@ -18,14 +18,14 @@ for n, nh, g, acc in [(4096, 65, 'l1', 'CD'), (4096, 65, 'l1', 'BT'), (5000, 64,
         kw = dict(max_iter=300, min_iter=5, accuracy_threshold=3e-3, dtype=dtype)
         s0, e0, d0 = solve('0', n, nh, g, acc, **kw)
         s1, e1, d1 = solve('1', n, nh, g, acc, **kw)
-        same = np.array_equal(e0['iterand'], e1['iterand']) and np.array_equal(e0['past_aux'], e1['past_aux']) and s0.iter == s1.iter
+        err = max(np.linalg.norm(e0[k].astype(float) - e1[k].astype(float)) / np.linalg.norm(e0[k].astype(float)) for k in ('iterand', 'past_aux'))
+        same = err < (1e-12 if dtype == 'float64' else 1e-4) and s0.iter == s1.iter and e0['past_t'] == e1['past_t']
         r0, r1 = np.asarray(d0['Relative Improvement'], float)[1:], np.asarray(d1['Relative Improvement'], float)[1:]
-        close = np.allclose(r0, r1, rtol=1e-12)
+        close = len(r0) == len(r1) and np.allclose(r0, r1, rtol=1e-9 if dtype == 'float64' else 1e-2)
         ok &= same and close
-        print(f'n={n} nh={nh} {g} {acc} {dtype}: updates {s0.iter}/{s1.iter} iterates bitwise {same} diag close {close}')
+        print(f'n={n} nh={nh} {g} {acc} {dtype}: updates {s0.iter}/{s1.iter} rel diff {err:.1e} ok {same} diag close {close}')
 print('ALL OK' if ok else 'MISMATCH')
-for flag, nt in (("0", "0"), ("1", "128"), ("1", "256")):
-    os.environ["PCS_APGD_CLUSTER_NT"] = nt
+for flag, nt in (("0", "-"), ("1", "128")):
     os.environ['PCS_APGD_CLUSTER'] = flag
     for dtype in ('float64', 'float32'):
         kw = dict(max_iter=499, min_iter=499, accuracy_threshold=0)
