@@ -258,12 +258,18 @@ int pcs_cps_mri_ball_step_c128(void* u_out, void* spec_next, const void* u, cons
 /* ---- a whole AcceleratedProximalGradientDescent solve in one launch: the loop of core/solver.py:55-76 with
  *      update_iterand / update_diagnostics / stopping_metric of opt/proxalgs.py:586-622, for
  *        F = 1/2||h * x - y||^2 (flat Convolve1D, linop/conv.py:20-164), G = none | g_param-threshold L1 | nonneg.
- *   One block keeps the problem in shared memory (n <= pcs_apgd_conv1d_run_max_n(); at most 256 taps) and runs updates it0, it0+1, ...
- *   while (it <= max_iter and ||x'-x||/||x|| > threshold) or it <= min_iter, exactly as the reference does.
+ *   The problem stays in shared memory (n <= pcs_apgd_conv1d_run_max_n(); at most 256 taps): of one block, or -- n >= 2048 on a
+ *   device that can place a cluster of 16 or 8 blocks, unless PCS_APGD_CLUSTER=0 -- split over the blocks of one thread-block
+ *   cluster, which hand edge values to their neighbours through distributed shared memory.  Either way the launch runs
+ *   updates it0, it0+1, ... while (it <= max_iter and ||x'-x||/||x|| > threshold) or it <= min_iter, exactly as the reference
+ *   does (the cluster kernel starts an update before the sums behind the test are in and drops it if they say stop).
  *   g_mode 0 none, 1 L1 (g_param = tau * lambda), 2 NonNegativeOrthant.  accel 0 none, 1 'BT', 2 'CD' (parameter d).
  *   x_inout / aux_inout: iterate and past_aux (in: start, out: result).  diag_out_f64: one row of 4 doubles per update
  *   (||x'-x||^2, ||x||^2, 0, 0).  n_iter_out_i64[0] = update index after the loop, [1] = final t (raw double bits). */
 int64_t pcs_apgd_conv1d_run_max_n(void);
+/* What this host thread's last pcs_apgd_conv1d_run launched: out4_host = {kernel (0 single block, 1 cluster), blocks,
+ * threads per block, elements per thread}.  Diagnostic only (the parity tests assert on it). */
+int pcs_apgd_last_launch(int64_t* out4_host);
 PCS_DECL_REAL(pcs_apgd_conv1d_run,
               (void* x_inout, void* aux_inout, const void* y, const void* h, int nh, int offset, int64_t n, int g_mode,
                double g_param, double tau, int accel, double d, double t0, int64_t it0, int64_t max_iter,

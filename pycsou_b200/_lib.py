@@ -90,6 +90,7 @@ PLAIN = {
     'pcs_reduce_workspace_bytes': ([], I64),
     'pcs_pds_tv_workspace_bytes': ([], I64),
     'pcs_pds_tv_last_launch': ([P], I32),
+    'pcs_apgd_last_launch': ([P], I32),
     # peer (NVLink) memory for the slab-decomposed solvers (csrc/pcs_peer.cu)
     'pcs_peer_handle_bytes': ([], I32),
     'pcs_peer_alloc': ([P, I64, P], I32),

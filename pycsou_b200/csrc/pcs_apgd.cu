@@ -519,6 +519,9 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
     cluster.sync();                                              // ... and that holds for every block: nothing is in flight when one leaves
 }
 
+// what the last pcs_apgd_conv1d_run call of this host thread launched (pcs_apgd_last_launch; tests assert on it)
+thread_local int64_t g_apgd_last[4] = {-1, 0, 0, 0};   // kernel (0 single block, 1 cluster), blocks, threads per block, elements per thread
+
 // Returns -1 when the cluster kernel cannot run this problem (the caller falls back to the single-block kernel).
 template <typename T, int EPT, int APC_NT> int apgd_cluster_launch(const ApgdArgs<T>& A, int CL, cudaStream_t s) {
     constexpr int M = APC_NT * EPT;
@@ -544,6 +547,7 @@ template <typename T, int EPT, int APC_NT> int apgd_cluster_launch(const ApgdArg
         (void)cudaGetLastError();
         return -1;
     }
+    g_apgd_last[0] = 1; g_apgd_last[1] = CL; g_apgd_last[2] = APC_NT; g_apgd_last[3] = EPT;
     return check_launch("pcs_apgd_conv1d_run");
 }
 template <typename T> int apgd_cluster_try(const ApgdArgs<T>& A, cudaStream_t s) {
@@ -563,6 +567,7 @@ template <typename T> int apgd_cluster_try(const ApgdArgs<T>& A, cudaStream_t s)
 template <typename T, int EPT, int NT> int apgd_launch(const ApgdArgs<T>& A, size_t smem, cudaStream_t s) {
     cudaFuncSetAttribute(apgd_run_kernel<T, EPT, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     apgd_run_kernel<T, EPT, NT><<<1, NT, smem, s>>>(A);
+    g_apgd_last[0] = 0; g_apgd_last[1] = 1; g_apgd_last[2] = NT; g_apgd_last[3] = EPT;
     return check_launch("pcs_apgd_conv1d_run");
 }
 
@@ -599,6 +604,11 @@ int pcs_apgd_conv1d_run_impl(T* x, T* aux, const T* y, const T* h, int nh, int o
 }  // namespace
 
 extern "C" int64_t pcs_apgd_conv1d_run_max_n(void) { return (int64_t)APGD_MAX_N; }
+extern "C" int pcs_apgd_last_launch(int64_t* out4) {
+    if (!out4) return PCS_ERR_ARG;
+    for (int i = 0; i < 4; ++i) out4[i] = g_apgd_last[i];
+    return PCS_OK;
+}
 
 PCS_EXPORT_REAL(pcs_apgd_conv1d_run,
                 (void* x_inout, void* aux_inout, const void* y, const void* h, int nh, int offset, int64_t n, int g_mode,

@@ -452,6 +452,15 @@ def plan_pds(solver):
         return None
 
 
+def apgd_last_launch():
+    """Kernel and launch geometry of this thread's last one-launch APGD solve (``pcs_apgd_last_launch``)."""
+    out = np.zeros(4, dtype=np.int64)
+    _lib.check(_lib.call_plain('pcs_apgd_last_launch', out.ctypes.data_as(C.c_void_p)))
+    d = dict(zip(('kernel', 'blocks', 'threads', 'per_thread'), (int(v) for v in out)))
+    d['kernel'] = {0: 'apgd_run_kernel', 1: 'apgd_cluster_kernel'}.get(d['kernel'], 'none')
+    return d
+
+
 class ApgdConv1dPlan:
     """Whole-solve plan for ``APGD`` with ``F = 1/2 ||h * x - y||^2`` on a flat vector (``csrc/pcs_apgd.cu``)."""
 

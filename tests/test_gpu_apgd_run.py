@@ -86,3 +86,56 @@ def test_run_fp32_continuation_and_verbose_path():
     s3, _, _ = _build(2048, 33, 'l1', 'CD', **kw)
     full, _, _ = s3.iterate()
     assert isinstance(last['iterand'], np.ndarray) and rel_l2(last['iterand'], full['iterand']) < 1e-13
+
+
+def _solve(cluster, *a, **kw):
+    import os
+    from pycsou_b200.opt._fused import apgd_last_launch
+    old = os.environ.get('PCS_APGD_CLUSTER')
+    os.environ['PCS_APGD_CLUSTER'] = '1' if cluster else '0'
+    try:
+        s, Fo, Go = _build(*a, **kw)
+        est, _, diag = s.iterate()
+        return s, est, np.asarray(diag['Relative Improvement'], dtype=float), apgd_last_launch(), (Fo, Go)
+    finally:
+        if old is None:
+            del os.environ['PCS_APGD_CLUSTER']
+        else:
+            os.environ['PCS_APGD_CLUSTER'] = old
+
+
+@pytest.mark.parametrize('n,nh,gname,acc', [(4096, 65, 'l1', 'CD'), (4096, 64, 'l1', 'BT'), (2048, 33, 'nonneg', None),
+                                            (2049, 9, 'none', 'BT'), (8191, 255, 'l1', 'CD'), (3000, 1, 'l1', 'CD'),
+                                            (6000, 200, 'nonneg', 'CD'), (8192, 129, 'l1', 'CD')])
+@pytest.mark.parametrize('dtype', ['float64', 'float32'])
+def test_cluster_kernel_equals_single_block_kernel(n, nh, gname, acc, dtype):
+    """The thread-block-cluster kernel (n >= 2048) against the single-block one: same number of updates under the live
+    stop test (the cluster kernel starts an update before the sums of the previous one are in and drops it if they say
+    stop), same diagnostics, iterates equal up to the order in which the taps are added."""
+    kw = dict(max_iter=300, min_iter=5, accuracy_threshold=3e-3, dtype=dtype)
+    s0, e0, r0, L0, _ = _solve(False, n, nh, gname, acc, **kw)
+    s1, e1, r1, L1, _ = _solve(True, n, nh, gname, acc, **kw)
+    assert L0['kernel'] == 'apgd_run_kernel' and L0['blocks'] == 1
+    assert L1['kernel'] == 'apgd_cluster_kernel' and L1['blocks'] in (8, 16) and L1['threads'] == 128
+    assert s0.iter == s1.iter and e0['past_t'] == e1['past_t'] and len(r0) == len(r1)
+    tol = 1e-12 if dtype == 'float64' else 1e-4
+    assert rel_l2(e1['iterand'], e0['iterand']) < tol and rel_l2(e1['past_aux'], e0['past_aux']) < tol
+    assert np.allclose(r1[1:], r0[1:], rtol=1e-9 if dtype == 'float64' else 1e-2)
+
+
+@pytest.mark.parametrize('kw', [dict(max_iter=40, min_iter=0, accuracy_threshold=0.0),        # runs into max_iter
+                                dict(max_iter=300, min_iter=0, accuracy_threshold=5e-2),     # stops early: an update is dropped
+                                dict(max_iter=3, min_iter=25, accuracy_threshold=1e9),       # min_iter forces updates past the test
+                                dict(max_iter=300, min_iter=0, accuracy_threshold=np.inf),   # inf > inf is false: no update at all
+                                dict(max_iter=0, min_iter=0, accuracy_threshold=0.0)])       # exactly one update
+def test_cluster_kernel_loop_condition(kw):
+    """core/solver.py:65-66 in the cluster kernel: every way the loop can end, against the oracle."""
+    s, est, ri, L, (Fo, Go) = _solve(True, 4096, 65, 'l1', 'CD', **kw)
+    xo, auxo, to, diago, no = O.apgd_iterate(4096, F=Fo, G=Go, tau=1.0, acceleration='CD', beta=1.0, **kw)
+    assert s.iter == no
+    if no > 0:
+        assert L['kernel'] == 'apgd_cluster_kernel'
+    assert rel_l2(est['iterand'], xo) < 1e-10 if np.linalg.norm(xo) else not np.any(est['iterand'])
+    assert np.isclose(est['past_t'], to, rtol=1e-15)
+    rio = np.asarray(diago['Relative Improvement'], dtype=float)
+    assert len(ri) == len(rio) and np.allclose(ri[1:], rio[1:], rtol=1e-7)
