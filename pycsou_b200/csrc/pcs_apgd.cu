@@ -307,12 +307,14 @@ template <typename T> __device__ __forceinline__ T tap_tree(const T (&a)[APGD_C]
     static_assert(APGD_C == 8, "tap_tree is written for groups of 8 taps");
     return ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
 }
+constexpr int APC_BLOCK = 160;     // four warps of filter passes + one warp for everything scalar
 template <typename T, int EPT, int APC_NT>
-__global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<T> A) {
+__global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdArgs<T> A) {
+    static_assert(APC_NT == 128 && APC_BLOCK == APC_NT + 32 && EPT % 2 == 0, "four pass warps, one scalar warp, pair-aligned windows");
     extern __shared__ __align__(16) unsigned char smem[];
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = (int)cluster.block_rank(), CL = (int)cluster.num_blocks();
-    constexpr int C = APGD_C, M = APC_NT * EPT, NW = APC_NT / 32;
+    constexpr int C = APGD_C, M = APC_NT * EPT;
     const int n = A.n, off = A.offset;
     const int nhp = (A.nh + C - 1) / C * C;
     const int EXW = nhp + C;                                   // elements stored into a neighbour's halo (<= M, checked by the host)
@@ -321,19 +323,24 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
     T* const bx = reinterpret_cast<T*>(smem);                  // iterate: halo | own | halo
     T* const br = bx + LEN;                                    // residual, same layout
     T* const sh = br + LEN;                                    // taps, zero padded to nhp
-    double* const parts = reinterpret_cast<double*>(smem + ((size_t)(2 * LEN + APGD_MAX_TAPS) * sizeof(T) + 15) / 16 * 16);   // [4][16][warps][2]
-    unsigned long long* const bars = reinterpret_cast<unsigned long long*>(parts + 4 * APC_MAXCL * NW * 2);   // x halo, r halo, sums[4]
+    double* const parts = reinterpret_cast<double*>(smem + ((size_t)(2 * LEN + APGD_MAX_TAPS) * sizeof(T) + 15) / 16 * 16);   // [4 sets][16 blocks][2]
+    double2* const psum = reinterpret_cast<double2*>(parts + 4 * APC_MAXCL * 2);      // [128]: the pass threads' sums of one update
+    double* const scal = reinterpret_cast<double*>(psum + APC_NT);                   // [2][2]: momentum scalars a, 1 + a of two updates
+    unsigned long long* const bars = reinterpret_cast<unsigned long long*>(scal + 4); // x halo, r halo, sums[4]
+    int* const dec = reinterpret_cast<int*>(bars + 6);                               // 1: the sums just looked at say stop
     T* const sx = bx + HP;                                     // own element j of this block at sx[j]
     T* const sr = br + HP;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int j0 = tid * EPT, g0 = rank * M + j0;              // local / global index of the thread's first element
+    const int tid = threadIdx.x, lane = tid & 31;
+    const bool scalar_warp = tid >= APC_NT;
+    const int j0 = (scalar_warp ? 0 : tid) * EPT, g0 = rank * M + j0;      // local / global index of a pass thread's first element
     const uint32_t bar_x = apc_smem_u32(bars), bar_r = bar_x + 8, bar_p = bar_x + 16;
     const bool has_l = rank > 0, has_r = rank + 1 < CL;
 
-    for (int i = tid; i < 2 * LEN + APGD_MAX_TAPS; i += APC_NT) reinterpret_cast<T*>(smem)[i] = T(0);
-    for (int i = tid; i < 4 * APC_MAXCL * NW * 2; i += APC_NT) parts[i] = 0.0;
+    for (int i = tid; i < 2 * LEN + APGD_MAX_TAPS; i += APC_BLOCK) reinterpret_cast<T*>(smem)[i] = T(0);
+    for (int i = tid; i < 4 * APC_MAXCL * 2; i += APC_BLOCK) parts[i] = 0.0;
     if (tid == 0) {
         for (int b = 0; b < 6; ++b) apc_mbar_init(bar_x + 8 * b, 1);
+        *dec = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     cluster.sync();                                            // nobody stores into memory that is still being cleared; barriers exist
@@ -341,12 +348,13 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
 #pragma unroll
     for (int e = 0; e < EPT; ++e) {
         const int i = g0 + e;
-        xa[e] = i < n ? A.x[i] : T(0);
-        pa[e] = i < n ? A.aux[i] : T(0);
-        ya[e] = i < n ? A.y[i] : T(0);
-        sx[j0 + e] = xa[e];
+        const bool in = !scalar_warp && i < n;
+        xa[e] = in ? A.x[i] : T(0);
+        pa[e] = in ? A.aux[i] : T(0);
+        ya[e] = in ? A.y[i] : T(0);
+        if (!scalar_warp) sx[j0 + e] = xa[e];
     }
-    for (int k = tid; k < A.nh; k += APC_NT) sh[k] = A.h[k];
+    for (int k = tid; k < A.nh; k += APC_BLOCK) sh[k] = A.h[k];
     // Where this block's edge values go: the same offsets in the neighbours' copies of the two arrays, and their barriers.
     const uint32_t lbx = has_l ? apc_mapa(apc_smem_u32(bx), rank - 1) : 0u, rbx = has_r ? apc_mapa(apc_smem_u32(bx), rank + 1) : 0u;
     const uint32_t lbr = has_l ? apc_mapa(apc_smem_u32(br), rank - 1) : 0u, rbr = has_r ? apc_mapa(apc_smem_u32(br), rank + 1) : 0u;
@@ -358,64 +366,85 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
         if (has_r && j >= M - EXW) apc_st_async(right + (uint32_t)((HP - EXW + (j - (M - EXW))) * sizeof(T)), v, rbar + bar_off);
     };
     const uint32_t hbytes = (uint32_t)(((has_l ? EXW : 0) + (has_r ? EXW : 0)) * sizeof(T));
-    const uint32_t pbytes = (uint32_t)(CL * NW * 2 * sizeof(double));
+    const uint32_t pbytes = (uint32_t)(CL * 2 * sizeof(double));
     const uint32_t my_parts = lane < CL ? apc_mapa(apc_smem_u32(parts), lane) : 0u, my_pbar = lane < CL ? apc_mapa(bar_p, lane) : 0u;
     if (tid == 0) apc_mbar_expect_tx(bar_x, hbytes);
+    if (!scalar_warp) {
 #pragma unroll
-    for (int e = 0; e < EPT; ++e) push(lbx, rbx, 0u, j0 + e, xa[e]);
-    __syncthreads();                                           // own part of sx and the taps are complete
-    uint32_t ph_x = 0, ph_r = 0, ph_p = 0;                     // phase parities (ph_p: bit b for set b of the sums)
-
-#ifdef APC_PHASE_TIMING
-    long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tk = clock64();
-#define APC_TICK(i) { const long long now_ = clock64(); ph[i] += now_ - tk; tk = now_; }
-#else
-#define APC_TICK(i)
-#endif
+        for (int e = 0; e < EPT; ++e) push(lbx, rbx, 0u, j0 + e, xa[e]);
+    }
+    uint32_t ph_x = 0, ph_r = 0, ph_p = 0;                     // phase parities (ph_p: bit b for set b of the sums; scalar warp)
     const T tau = A.tau;
     const StopTest stop(A.threshold);
-    double t_old = A.t0;
     long long it = A.it0;
-    bool pending = false;                                        // the sums of update it - 1 have not been looked at yet
-    // Adds the sums of update `upd` (set upd & 3) once they are all here, writes its row of diagnostics, returns the stop test.
+    // momentum (scalar warp): t_m = t of the last update applied, t_c = t of update `it`; a = (t_m - 1) / t_c
+    double t_m = A.t0, t_c = A.t0;
+    auto momentum = [&](long long upd, double t_before, double* slot) -> double {
+        double t;
+        if (A.accel == ACC_BT) t = (1.0 + sqrt(1.0 + 4.0 * t_before * t_before)) / 2.0;
+        else if (A.accel == ACC_CD) t = ((double)upd + A.d) / A.d;
+        else { t = 1.0; t_before = 1.0; }
+        const double a = (t_before - 1.0) / t;
+        if (lane == 0) { slot[0] = a; slot[1] = 1.0 + a; }
+        return t;
+    };
+    if (scalar_warp) t_c = momentum(it, t_m, scal + 2 * (int)((it - A.it0) & 1));
+    __syncthreads();                                           // own part of sx, the taps and the first momentum scalars are in place
+    // core/solver.py:65-66: update `it` runs when (it <= max_iter and metric(it - 1) > threshold) or it <= min_iter, the metric
+    // before the first update being inf.  The sums behind metric(it - 1) come from all blocks; waiting for them would put an
+    // all-to-all exchange and a chain of FP64 additions on the path of every update.  Instead the pass warps go straight on
+    // to update `it`, on the assumption that the metric was above the threshold, while the scalar warp adds the block's sums
+    // of update it - 1, exchanges them, adds all blocks' and sets `dec`; after update `it` everybody looks at `dec`, and if
+    // it says stop the update is dropped (the pass threads keep the state before it in registers).  What the caller gets
+    // -- iterates, number of updates, diagnostics -- is what the reference's loop gives.
+    // Adds the pass threads' sums of update `upd` and sends the block's two sums to slot `rank` of set upd & 3 of every block.
+    auto send_sums = [&](long long upd) {
+        const unsigned set = (unsigned)(upd - A.it0) & 3u;
+        if (lane == 0) apc_mbar_expect_tx(bar_p + 8 * set, pbytes);
+        double s_d = 0.0, s_x = 0.0;
+#pragma unroll
+        for (int c = 0; c < APC_NT / 32; ++c) {
+            const double2 v = psum[lane + 32 * c];
+            s_d += v.x;
+            s_x += v.y;
+        }
+        s_d = warp_sum(s_d);
+        s_x = warp_sum(s_x);
+        if (lane < CL) {
+            const uint32_t slot = (uint32_t)((set * APC_MAXCL + rank) * 2 * sizeof(double));
+            apc_st_async(my_parts + slot, s_d, my_pbar + 8 * set);
+            apc_st_async(my_parts + slot + 8, s_x, my_pbar + 8 * set);
+        }
+    };
+    // Adds all blocks' sums of update `upd` once they are here (same slots, same order in every block), writes the row of
+    // diagnostics, returns the stop test.
     auto settle = [&](long long upd) -> bool {
         const unsigned set = (unsigned)(upd - A.it0) & 3u;
         apc_mbar_wait(bar_p + 8 * set, (ph_p >> set) & 1u);
         ph_p ^= 1u << set;
-        const double* pp = parts + (size_t)set * APC_MAXCL * NW * 2;
-        double s_d = 0.0, s_x = 0.0;
-#pragma unroll
-        for (int c = 0; c < APC_MAXCL * NW / 32; ++c) {          // (slots of absent blocks stay zero)
-            s_d += pp[2 * (lane + 32 * c)];
-            s_x += pp[2 * (lane + 32 * c) + 1];
-        }
-        s_d = warp_sum(s_d);                                     // same slots, same order in every warp of every block
+        const double* pp = parts + (size_t)set * APC_MAXCL * 2;
+        double s_d = lane < APC_MAXCL ? pp[2 * lane] : 0.0, s_x = lane < APC_MAXCL ? pp[2 * lane + 1] : 0.0;   // (absent blocks: zero)
+        s_d = warp_sum(s_d);
         s_x = warp_sum(s_x);
-        if (rank == 0 && tid == 0) {
+        if (rank == 0 && lane == 0) {
             double* row = A.diag + 4 * (upd - A.it0);
             row[0] = s_d; row[1] = s_x; row[2] = 0.0; row[3] = 0.0;
         }
         return stop.above(s_d, s_x);
     };
-    // core/solver.py:65-66: update `it` runs when (it <= max_iter and metric(it - 1) > threshold) or it <= min_iter, the metric
-    // before the first update being inf.  The sums behind metric(it - 1) come from all blocks, so waiting for them would put
-    // an all-to-all exchange on the path of every update; instead update `it` STARTS as soon as the neighbours' halos are in,
-    // on the assumption that the metric was above the threshold, and the sums of update it - 1 are looked at when update
-    // `it` is half done -- after its residual pass, while the neighbours' edge values of the residual are on their way; the
-    // sums arrived long before.  If they say stop, the update is dropped: the iterate has not been touched yet.  What the
-    // caller gets -- iterates, number of updates, diagnostics -- is what the reference's loop gives.
-    bool dropped = false;
+    T xk[EPT], pk[EPT];                                          // pass threads: the state before the update in flight
+    bool pending = false;                                        // the sums of update it - 1 have not been looked at yet
     bool go = (it <= A.max_iter && INFINITY > A.threshold) || it <= A.min_iter;
     while (go) {
-        const unsigned set = (unsigned)(it - A.it0) & 3u;
-        if (tid == 0) {
-            apc_mbar_expect_tx(bar_r, hbytes);
-            apc_mbar_expect_tx(bar_p + 8 * set, pbytes);
-        }
-        apc_mbar_wait(bar_x, ph_x);                              // the neighbours' edge values of x are in the halos
-        ph_x ^= 1u;
-        APC_TICK(3)
-        {   // residual r = h * x - y on the own segment; tap c of every group of C has its own running sum
+        double t_n = t_c;
+        if (scalar_warp) {
+            if (pending) send_sums(it - 1);
+            t_n = momentum(it + 1, t_c, scal + 2 * (int)((it + 1 - A.it0) & 1));      // for the next update
+        } else {
+            if (tid == 0) apc_mbar_expect_tx(bar_r, hbytes);
+            apc_mbar_wait(bar_x, ph_x);                          // the neighbours' edge values of x are in the halos
+            ph_x ^= 1u;
+            // residual r = h * x - y on the own segment; tap c of every group of C has its own running sum
             T acc[EPT][C];
 #pragma unroll
             for (int e = 0; e < EPT; ++e)
@@ -432,26 +461,19 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
                 push(lbr, rbr, 8u, j0 + e, rv);
             }
         }
-        APC_TICK(0)
-        __syncthreads();                                         // own part of sr complete (and every thread is past the wait on bar_x)
-        if (pending && !settle(it - 1) && it > A.min_iter) {     // the loop had ended before this update: drop it
-            dropped = true;
-            pending = false;
-            break;
-        }
-        APC_TICK(6)
-        if (tid == 0) apc_mbar_expect_tx(bar_x, hbytes);         // next update's x halos
-        double t, a;
-        if (A.accel == ACC_BT) t = (1.0 + sqrt(1.0 + 4.0 * t_old * t_old)) / 2.0;
-        else if (A.accel == ACC_CD) t = ((double)it + A.d) / A.d;
-        else { t = 1.0; t_old = 1.0; }
-        a = (t_old - 1.0) / t;
-        const T ta = (T)a, t1a = (T)(1.0 + a);
-        apc_mbar_wait(bar_r, ph_r);                              // the neighbours' edge values of r are in the halos
-        ph_r ^= 1u;
-        APC_TICK(1)
-        double s_d = 0.0, s_x = 0.0;
-        {
+        __syncthreads();                                         // A: own part of sr complete; every pass thread is past the wait on bar_x
+        if (scalar_warp) {
+            if (pending) {
+                const bool above = settle(it - 1);
+                if (lane == 0) *dec = above ? 0 : 1;
+            }
+        } else {
+            if (tid == 0) apc_mbar_expect_tx(bar_x, hbytes);     // next update's x halos
+            const double* my_scal = scal + 2 * (int)((it - A.it0) & 1);
+            const T ta = (T)my_scal[0], t1a = (T)my_scal[1];
+            apc_mbar_wait(bar_r, ph_r);                          // the neighbours' edge values of r are in the halos
+            ph_r ^= 1u;
+            double s_d = 0.0, s_x = 0.0;
             T g[EPT][C];
 #pragma unroll
             for (int e = 0; e < EPT; ++e)
@@ -461,6 +483,8 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
             else apc_tap_pass<T, EPT, 0, +1>(sr + j0 - off, sh, nhp, g);
 #pragma unroll
             for (int e = 0; e < EPT; ++e) {
+                xk[e] = xa[e];
+                pk[e] = pa[e];
                 if (g0 + e < n) {
                     const T v = xa[e] - mul_rn(tau, tap_tree(g[e]));
                     T p;
@@ -475,47 +499,45 @@ __global__ void __launch_bounds__(APC_NT, 1) apgd_cluster_kernel(const ApgdArgs<
                     xa[e] = xn;
                 }
             }
+#pragma unroll
+            for (int e = 0; e < EPT; ++e) {
+                sx[j0 + e] = xa[e];
+                push(lbx, rbx, 0u, j0 + e, xa[e]);
+            }
+            psum[tid] = make_double2(s_d, s_x);
         }
+        __syncthreads();                                         // B: own part of sx, the sums and `dec` complete; every pass thread is past the wait on bar_r
+        if (pending && *dec != 0 && it > A.min_iter) {           // the loop had ended before this update: drop it
+#pragma unroll
+            for (int e = 0; e < EPT; ++e) { xa[e] = xk[e]; pa[e] = pk[e]; }
+            pending = false;
+            break;
+        }
+        pending = true;
+        t_m = t_c;
+        t_c = t_n;
+        ++it;
+        go = it <= A.max_iter || it <= A.min_iter;               // (and the metric above the threshold: known one update later)
+    }
+    if (scalar_warp) {
+        if (pending) {                                           // the last update's row of diagnostics
+            send_sums(it - 1);
+            settle(it - 1);
+        }
+        if (rank == 0 && lane == 0) {
+            A.n_iter[0] = it;
+            A.n_iter[1] = __double_as_longlong(t_m);
+        }
+    } else {
 #pragma unroll
         for (int e = 0; e < EPT; ++e) {
-            sx[j0 + e] = xa[e];
-            push(lbx, rbx, 0u, j0 + e, xa[e]);
+            if (g0 + e < n) {
+                A.x[g0 + e] = xa[e];
+                A.aux[g0 + e] = pa[e];
+            }
         }
-        APC_TICK(2)
-        s_d = warp_sum(s_d);                                     // each WARP's partial sums go into slot (rank, warp) of every block
-        s_x = warp_sum(s_x);
-        if (lane < CL) {
-            const uint32_t slot = (uint32_t)(((set * APC_MAXCL + rank) * NW + warp) * 2 * sizeof(double));
-            apc_st_async(my_parts + slot, s_d, my_pbar + 8 * set);
-            apc_st_async(my_parts + slot + 8, s_x, my_pbar + 8 * set);
-        }
-        APC_TICK(4)
-        __syncthreads();                                         // own part of sx complete; every thread is past the wait on bar_r
-        pending = true;
-        t_old = t;
-        ++it;
-        go = it <= A.max_iter || it <= A.min_iter;               // (and the metric above the threshold: settled after the update)
-        APC_TICK(5)
+        apc_mbar_wait(bar_x, ph_x);                              // everything sent to this block's halos has arrived ...
     }
-    if (pending) settle(it - 1);                                 // the last update's row of diagnostics
-#ifdef APC_PHASE_TIMING
-    if (tid == 0 && (rank == 1 || rank == CL - 1))
-        printf("apgd cluster rank %d: %lld updates; cycles per update: residual %lld, wait r %lld, gradient+prox %lld, wait x %lld, sums+push %lld, tail %lld, sync+settle %lld\n",
-               rank, it - A.it0, ph[0] / (it - A.it0), ph[1] / (it - A.it0), ph[2] / (it - A.it0), ph[3] / (it - A.it0), ph[4] / (it - A.it0),
-               ph[5] / (it - A.it0), ph[6] / (it - A.it0));
-#endif
-#pragma unroll
-    for (int e = 0; e < EPT; ++e) {
-        if (g0 + e < n) {
-            A.x[g0 + e] = xa[e];
-            A.aux[g0 + e] = pa[e];
-        }
-    }
-    if (rank == 0 && tid == 0) {
-        A.n_iter[0] = it;
-        A.n_iter[1] = __double_as_longlong(t_old);
-    }
-    apc_mbar_wait(dropped ? bar_r : bar_x, dropped ? ph_r : ph_x);   // everything sent to this block has arrived ...
     cluster.sync();                                              // ... and that holds for every block: nothing is in flight when one leaves
 }
 
@@ -525,7 +547,7 @@ thread_local int64_t g_apgd_last[4] = {-1, 0, 0, 0};   // kernel (0 single block
 // Returns -1 when the cluster kernel cannot run this problem (the caller falls back to the single-block kernel).
 template <typename T, int EPT, int APC_NT> int apgd_cluster_launch(const ApgdArgs<T>& A, int CL, cudaStream_t s) {
     constexpr int M = APC_NT * EPT;
-    const size_t smem = ((size_t)(2 * (M + 2 * APGD_PAD) + APGD_MAX_TAPS) * sizeof(T) + 15) / 16 * 16 + (4 * 2 * APC_MAXCL * (APC_NT / 32)) * sizeof(double) + 6 * sizeof(unsigned long long);
+    const size_t smem = ((size_t)(2 * (M + 2 * APGD_PAD) + APGD_MAX_TAPS) * sizeof(T) + 15) / 16 * 16 + (4 * 2 * APC_MAXCL + 2 * APC_NT + 4) * sizeof(double) + 6 * sizeof(unsigned long long) + 16;
     auto kern = apgd_cluster_kernel<T, EPT, APC_NT>;
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
         cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
@@ -533,7 +555,7 @@ template <typename T, int EPT, int APC_NT> int apgd_cluster_launch(const ApgdArg
         return -1;
     }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)CL); cfg.blockDim = dim3(APC_NT); cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cfg.gridDim = dim3((unsigned)CL); cfg.blockDim = dim3(APC_BLOCK); cfg.dynamicSmemBytes = smem; cfg.stream = s;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = (unsigned)CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
@@ -547,7 +569,7 @@ template <typename T, int EPT, int APC_NT> int apgd_cluster_launch(const ApgdArg
         (void)cudaGetLastError();
         return -1;
     }
-    g_apgd_last[0] = 1; g_apgd_last[1] = CL; g_apgd_last[2] = APC_NT; g_apgd_last[3] = EPT;
+    g_apgd_last[0] = 1; g_apgd_last[1] = CL; g_apgd_last[2] = APC_BLOCK; g_apgd_last[3] = EPT;
     return check_launch("pcs_apgd_conv1d_run");
 }
 template <typename T> int apgd_cluster_try(const ApgdArgs<T>& A, cudaStream_t s) {

@@ -116,7 +116,7 @@ def test_cluster_kernel_equals_single_block_kernel(n, nh, gname, acc, dtype):
     s0, e0, r0, L0, _ = _solve(False, n, nh, gname, acc, **kw)
     s1, e1, r1, L1, _ = _solve(True, n, nh, gname, acc, **kw)
     assert L0['kernel'] == 'apgd_run_kernel' and L0['blocks'] == 1
-    assert L1['kernel'] == 'apgd_cluster_kernel' and L1['blocks'] in (8, 16) and L1['threads'] == 128
+    assert L1['kernel'] == 'apgd_cluster_kernel' and L1['blocks'] in (8, 16) and L1['threads'] == 160
     assert s0.iter == s1.iter and e0['past_t'] == e1['past_t'] and len(r0) == len(r1)
     tol = 1e-12 if dtype == 'float64' else 1e-4
     assert rel_l2(e1['iterand'], e0['iterand']) < tol and rel_l2(e1['past_aux'], e0['past_aux']) < tol
