@@ -228,19 +228,28 @@ __global__ void __launch_bounds__(NT, 1) apgd_run_kernel(const ApgdArgs<T> A) {
 
 // ---- the same solve on a CLUSTER of thread blocks --------------------------------------------------------------------------
 // One SM bounds the single-block kernel: at N = 4096 with a 65-tap filter an update is 532 k FP64 multiply-adds = 4.4 us of one
-// SM's FP64 pipe (11.5 us measured).  Here a thread-block cluster (16 blocks, 8 if the device cannot place 16) shares the
-// vector: block c owns M = NT EPT consecutive elements and keeps them (and the residual) in ITS shared memory with a halo
-// on either side.  The thread that computes an element near the edge of the segment also stores it into the neighbour's
-// halo with st.async -- a store through distributed shared memory that counts its bytes on an mbarrier in the RECEIVING
-// block -- so a block waits only for its own two neighbours and only for the bytes it is about to read.  (A cluster
-// barrier with release semantics costs a MEMBAR.ALL.GPU per arrival: 0.9-1.5 k cycles per barrier, two per update, were
-// half the time of the first version of this kernel.)  No signal is needed in the other direction: a block can only be
-// sent new halo values by a neighbour that has received the values computed FROM the old ones, and the threads that read
-// a halo are among those that send the edge values (EXW below covers the filter's reach).
-// The stop test stays live: each warp's two partial sums go by the same kind of store into a slot of EVERY block (two
-// sets of slots, alternating, because a fast block may send the next update's sums while a slow one still reads), and
-// all blocks add the slots in the same order -- the same decision everywhere, no global memory, no host.  Per element
-// the operations are those of the single-block kernel, in the same order; only the two sums are added in another order.
+// SM's FP64 pipe (11.4 us measured).  Here a thread-block cluster (16 blocks, 8 if the device cannot place 16) shares the
+// vector: block c owns M = 128 EPT consecutive elements and keeps them (and the residual) in ITS shared memory with a halo
+// on either side.
+// * Neighbours.  The thread that computes an element within the filter's reach of the edge of the segment also stores it
+//   into the neighbour's halo with st.async -- a store through distributed shared memory that counts its bytes on an
+//   mbarrier in the RECEIVING block -- so a block waits only for its own two neighbours and only for the bytes it is about
+//   to read.  (A cluster barrier with release semantics is a MEMBAR.ALL.GPU per arrival: 0.9-1.5 k cycles per barrier, two
+//   per update, were half the time of the first version of this kernel.)  No signal is needed in the other direction: a
+//   block can only be sent new halo values by a neighbour that has received the values computed FROM the old ones, and
+//   the threads that read a halo are the ones that send the edge values that neighbour is waiting for.
+// * Passes.  Four warps run the two filter passes, 2 or 4 consecutive elements per thread.  What bounds a pass is shared-
+//   memory wavefronts, not the FP64 pipe (16 blocks leave each SM 1/16 of the multiply-adds but every thread still reads
+//   a window of samples per group of taps): the window is read as aligned pairs (apc_tap_pass), and each of the C tap
+//   positions of a group has its own running sum, added at the end in a fixed tree.  So the taps of an element are not
+//   added in the single-block kernel's order: iterates agree with it to rounding (1e-15 relative in fp64), not bit for bit.
+// * Everything scalar is the FIFTH warp's: the momentum scalars of the next update (two FP64 divisions, a square root),
+//   the block's sums of the last update (from the pass threads' partial sums in shared memory), their exchange -- the same
+//   kind of store into slot `rank` of EVERY block; four sets of slots in turn, because a block may be up to two updates
+//   ahead of another -- the sum of all blocks' slots in one order everywhere, the row of diagnostics and the stop test.
+//   The pass warps do not wait for any of it: they start update `it` as soon as the neighbours' halos are in, and look at
+//   the stop test of update it - 1 when update `it` is done; if it says stop the update is dropped (its input state is
+//   still in registers).  The stop test is live and exact, but off the path of the updates; no global memory, no host.
 __device__ __forceinline__ uint32_t apc_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ uint32_t apc_mapa(uint32_t addr, int rank) {
     uint32_t r;
@@ -317,7 +326,6 @@ __global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdAr
     constexpr int C = APGD_C, M = APC_NT * EPT;
     const int n = A.n, off = A.offset;
     const int nhp = (A.nh + C - 1) / C * C;
-    const int EXW = nhp + C;                                   // elements stored into a neighbour's halo (<= M, checked by the host)
     constexpr int HP = APGD_PAD;
     constexpr int LEN = M + 2 * HP;
     T* const bx = reinterpret_cast<T*>(smem);                  // iterate: halo | own | halo
@@ -359,19 +367,26 @@ __global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdAr
     const uint32_t lbx = has_l ? apc_mapa(apc_smem_u32(bx), rank - 1) : 0u, rbx = has_r ? apc_mapa(apc_smem_u32(bx), rank + 1) : 0u;
     const uint32_t lbr = has_l ? apc_mapa(apc_smem_u32(br), rank - 1) : 0u, rbr = has_r ? apc_mapa(apc_smem_u32(br), rank + 1) : 0u;
     const uint32_t lbar = has_l ? apc_mapa(bar_x, rank - 1) : 0u, rbar = has_r ? apc_mapa(bar_x, rank + 1) : 0u;   // (+8: their bar_r)
-    // local element j goes to the right halo of the block on the left when j < EXW, to the left halo of the block on the
-    // right when j >= M - EXW
-    auto push = [&](uint32_t left, uint32_t right, uint32_t bar_off, int j, T v) {
-        if (has_l && j < EXW) apc_st_async(left + (uint32_t)((HP + M + j) * sizeof(T)), v, lbar + bar_off);
-        if (has_r && j >= M - EXW) apc_st_async(right + (uint32_t)((HP - EXW + (j - (M - EXW))) * sizeof(T)), v, rbar + bar_off);
+    // Only what a neighbour's filter really reaches is sent: its residual pass reads x up to `off` elements to its right and
+    // nh - 1 - off to its left, its gradient pass reads r nh - 1 - off to its right and `off` to its left.  (The passes also
+    // read up to nhp + C samples away under the zero taps that pad the filter: those only have to be finite, and what
+    // lies there -- zeros, or a value of some earlier update -- is.)  Local element j goes to the right halo of the block
+    // on the left when j < wl, to the left halo of the block on the right when j >= M - wr.
+    const int reach_a = off, reach_b = A.nh - 1 - off;
+    auto push = [&](uint32_t left, uint32_t right, uint32_t bar_off, int wl, int wr, int j, T v) {
+        if (has_l && j < wl) apc_st_async(left + (uint32_t)((HP + M + j) * sizeof(T)), v, lbar + bar_off);
+        if (has_r && j >= M - wr) apc_st_async(right + (uint32_t)((HP + j - M) * sizeof(T)), v, rbar + bar_off);
     };
-    const uint32_t hbytes = (uint32_t)(((has_l ? EXW : 0) + (has_r ? EXW : 0)) * sizeof(T));
+    // bytes a block receives per exchange: x from the left block's last reach_b and the right block's first reach_a
+    // elements; r from the left block's last reach_a and the right block's first reach_b
+    const uint32_t xbytes = (uint32_t)(((has_l ? reach_b : 0) + (has_r ? reach_a : 0)) * sizeof(T));
+    const uint32_t rbytes = (uint32_t)(((has_l ? reach_a : 0) + (has_r ? reach_b : 0)) * sizeof(T));
     const uint32_t pbytes = (uint32_t)(CL * 2 * sizeof(double));
     const uint32_t my_parts = lane < CL ? apc_mapa(apc_smem_u32(parts), lane) : 0u, my_pbar = lane < CL ? apc_mapa(bar_p, lane) : 0u;
-    if (tid == 0) apc_mbar_expect_tx(bar_x, hbytes);
+    if (tid == 0) apc_mbar_expect_tx(bar_x, xbytes);
     if (!scalar_warp) {
 #pragma unroll
-        for (int e = 0; e < EPT; ++e) push(lbx, rbx, 0u, j0 + e, xa[e]);
+        for (int e = 0; e < EPT; ++e) push(lbx, rbx, 0u, reach_a, reach_b, j0 + e, xa[e]);
     }
     uint32_t ph_x = 0, ph_r = 0, ph_p = 0;                     // phase parities (ph_p: bit b for set b of the sums; scalar warp)
     const T tau = A.tau;
@@ -441,7 +456,7 @@ __global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdAr
             if (pending) send_sums(it - 1);
             t_n = momentum(it + 1, t_c, scal + 2 * (int)((it + 1 - A.it0) & 1));      // for the next update
         } else {
-            if (tid == 0) apc_mbar_expect_tx(bar_r, hbytes);
+            if (tid == 0) apc_mbar_expect_tx(bar_r, rbytes);
             apc_mbar_wait(bar_x, ph_x);                          // the neighbours' edge values of x are in the halos
             ph_x ^= 1u;
             // residual r = h * x - y on the own segment; tap c of every group of C has its own running sum
@@ -458,7 +473,7 @@ __global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdAr
                 const T s = tap_tree(acc[e]);
                 const T rv = (g0 + e < n) ? s - ya[e] : T(0);
                 sr[j0 + e] = rv;
-                push(lbr, rbr, 8u, j0 + e, rv);
+                push(lbr, rbr, 8u, reach_b, reach_a, j0 + e, rv);
             }
         }
         __syncthreads();                                         // A: own part of sr complete; every pass thread is past the wait on bar_x
@@ -468,7 +483,7 @@ __global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdAr
                 if (lane == 0) *dec = above ? 0 : 1;
             }
         } else {
-            if (tid == 0) apc_mbar_expect_tx(bar_x, hbytes);     // next update's x halos
+            if (tid == 0) apc_mbar_expect_tx(bar_x, xbytes);     // next update's x halos
             const double* my_scal = scal + 2 * (int)((it - A.it0) & 1);
             const T ta = (T)my_scal[0], t1a = (T)my_scal[1];
             apc_mbar_wait(bar_r, ph_r);                          // the neighbours' edge values of r are in the halos
@@ -502,7 +517,7 @@ __global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdAr
 #pragma unroll
             for (int e = 0; e < EPT; ++e) {
                 sx[j0 + e] = xa[e];
-                push(lbx, rbx, 0u, j0 + e, xa[e]);
+                push(lbx, rbx, 0u, reach_a, reach_b, j0 + e, xa[e]);
             }
             psum[tid] = make_double2(s_d, s_x);
         }
