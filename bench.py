@@ -550,11 +550,12 @@ def parity_mode_measure(args, psf, y64, D, slab):
 
 # ------------------------------------------------------------------------------------------------ C1 / C2 (single GPU)
 def c1_measure():
-    """BASELINE.json configs[0]: 1-D LASSO, N = 4096 fp64, APGD('CD'), exactly 500 updates (one persistent launch)."""
+    """BASELINE.json configs[0]: 1-D LASSO, N = 4096 fp64, APGD('CD'), exactly 500 updates (one launch on a 16-block cluster)."""
     import torch
     from pycsou_b200.func.loss import SquaredL2Loss
     from pycsou_b200.func.penalty import L1Norm
     from pycsou_b200.linop.conv import Convolve1D
+    from pycsou_b200.opt._fused import apgd_last_launch
     from pycsou_b200.opt.proxalgs import APGD
     from pycsou_b200.util import synth
     _, h, y = synth.spikes_1d(4096, 32, 0)
@@ -571,9 +572,11 @@ def c1_measure():
         ms_solve = ms / 5
         alg = 5 * N * (4 if tag == 'f32' else 8)
         out[tag] = {'solve_ms': ms_solve, 'iter_per_s': 500 / (ms_solve * 1e-3), 'us_per_update': 1e3 * ms_solve / 500,
-                    'solver_path': type(s._plan).__name__ if s._plan is not None else 'generic'}
-    out['what'] = ('500 APGD updates, N=4096, one persistent-block launch per solve; latency bound (the state lives in one '
-                   "SM's shared memory; algorithmic HBM bytes are 5*N*s per SOLVE), no HBM roofline applies")
+                    'solver_path': type(s._plan).__name__ if s._plan is not None else 'generic',
+                    'kernel': apgd_last_launch()}
+    out['what'] = ('500 APGD updates, N=4096, ONE launch per solve on a thread-block cluster (16 SMs share the vector in '
+                   'their shared memory, neighbours exchange edge values through distributed shared memory, stop test '
+                   'live; DESIGN 3.7); latency bound (algorithmic HBM bytes are 5*N*s per SOLVE), no HBM roofline applies')
     return out
 
 
