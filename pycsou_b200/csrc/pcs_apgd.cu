@@ -270,13 +270,19 @@ __device__ __forceinline__ void apc_mbar_init(uint32_t bar, int count) {
 __device__ __forceinline__ void apc_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+// (try_wait suspends the thread for a while by itself.  Sixteen million failed tries in one wait can only be a bug: end the
+// launch with an error rather than hang the GPU.)
 __device__ __forceinline__ void apc_mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
-        "{\n\t.reg .pred p;\n\t"
+        "{\n\t.reg .pred p;\n\t.reg .u32 n;\n\t"
+        "mov.u32 n, 0;\n\t"
         "APC_WAIT_%=:\n\t"
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
         "@p bra APC_DONE_%=;\n\t"
-        "bra APC_WAIT_%=;\n\t"
+        "add.u32 n, n, 1;\n\t"
+        "setp.lt.u32 p, n, 0x1000000;\n\t"
+        "@p bra APC_WAIT_%=;\n\t"
+        "trap;\n\t"
         "APC_DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
 }
 constexpr int APC_MAXCL = 16;
