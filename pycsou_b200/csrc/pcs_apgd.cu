@@ -570,22 +570,27 @@ template <typename T, int EPT, int APC_NT> int apgd_cluster_launch(const ApgdArg
     constexpr int M = APC_NT * EPT;
     const size_t smem = ((size_t)(2 * (M + 2 * APGD_PAD) + APGD_MAX_TAPS) * sizeof(T) + 15) / 16 * 16 + (4 * 2 * APC_MAXCL + 2 * APC_NT + 4) * sizeof(double) + 6 * sizeof(unsigned long long) + 16;
     auto kern = apgd_cluster_kernel<T, EPT, APC_NT>;
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
-        cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
-        (void)cudaGetLastError();
-        return -1;
-    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)CL); cfg.blockDim = dim3(APC_BLOCK); cfg.dynamicSmemBytes = smem; cfg.stream = s;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = (unsigned)CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    int nclusters = 0;
-    if (cudaOccupancyMaxActiveClusters(&nclusters, kern, &cfg) != cudaSuccess || nclusters < 1) {
-        (void)cudaGetLastError();
-        return -1;
+    // Function attributes and the "can one such cluster be resident" query: once per device, kernel and cluster size
+    // (0 not asked yet, 1 yes, -1 no).  A race between host threads only repeats the calls.
+    static signed char ready[64][2];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return -1;
+    signed char& rdy = ready[dev][CL == 16 ? 0 : 1];
+    if (rdy == 0) {
+        int nclusters = 0;
+        const bool ok = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess &&
+                        cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess &&
+                        cudaOccupancyMaxActiveClusters(&nclusters, kern, &cfg) == cudaSuccess && nclusters >= 1;
+        if (!ok) (void)cudaGetLastError();
+        rdy = ok ? 1 : -1;
     }
+    if (rdy < 0) return -1;
     if (cudaLaunchKernelEx(&cfg, kern, A) != cudaSuccess) {
         (void)cudaGetLastError();
         return -1;

@@ -42,3 +42,18 @@ for flag, nt in (("0", "-"), ("1", "128")):
             best = min(best, a.elapsed_time(b))
         t0 = time.perf_counter(); s.reset(); s.iterate(); torch.cuda.synchronize(); t1 = time.perf_counter()
         print(f'cluster={flag} nt={nt} {dtype}: kernel {best:.3f} ms for 500 updates ({2 * best:.2f} us/update); iterate() {1e3 * (t1 - t0):.2f} ms')
+# stepping one update per launch (the iterates() generator): launch + set-up cost of the two kernels
+for flag in ('0', '1'):
+    os.environ['PCS_APGD_CLUSTER'] = flag
+    kw = dict(max_iter=499, min_iter=499, accuracy_threshold=0)
+    s, _, _ = _build(4096, 65, 'l1', 'CD', **kw)
+    s.iterate()
+    plan = s._plan
+    x, aux, t = s._init_state()
+    diag = torch.zeros(4, 4, dtype=torch.float64, device='cuda')
+    for _ in range(3): plan.run(x, aux, 1.0, 0, diag, single=True)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for k in range(200): x, aux, tt, it = plan.run(x, aux, 1.0, k, diag, single=True)
+    torch.cuda.synchronize()
+    print(f'cluster={flag}: one update per launch (with the read-back of n_iter): {1e6 * (time.perf_counter() - t0) / 200:.1f} us per update')
