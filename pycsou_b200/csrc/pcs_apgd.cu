@@ -453,6 +453,12 @@ __global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdAr
         }
         return stop.above(s_d, s_x);
     };
+#ifdef APC_PHASE_TIMING                                          // -DAPC_PHASE_TIMING: cycles per phase of a pass thread, printed by two blocks
+    long long ph[6] = {0, 0, 0, 0, 0, 0}, tk = clock64();
+#define APC_TICK(i) { const long long now_ = clock64(); ph[i] += now_ - tk; tk = now_; }
+#else
+#define APC_TICK(i)
+#endif
     T xk[EPT], pk[EPT];                                          // pass threads: the state before the update in flight
     bool pending = false;                                        // the sums of update it - 1 have not been looked at yet
     bool go = (it <= A.max_iter && INFINITY > A.threshold) || it <= A.min_iter;
@@ -465,6 +471,7 @@ __global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdAr
             if (tid == 0) apc_mbar_expect_tx(bar_r, rbytes);
             apc_mbar_wait(bar_x, ph_x);                          // the neighbours' edge values of x are in the halos
             ph_x ^= 1u;
+            APC_TICK(0)
             // residual r = h * x - y on the own segment; tap c of every group of C has its own running sum
             T acc[EPT][C];
 #pragma unroll
@@ -481,6 +488,7 @@ __global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdAr
                 sr[j0 + e] = rv;
                 push(lbr, rbr, 8u, reach_b, reach_a, j0 + e, rv);
             }
+            APC_TICK(1)
         }
         __syncthreads();                                         // A: own part of sr complete; every pass thread is past the wait on bar_x
         if (scalar_warp) {
@@ -489,11 +497,13 @@ __global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdAr
                 if (lane == 0) *dec = above ? 0 : 1;
             }
         } else {
+            APC_TICK(2)
             if (tid == 0) apc_mbar_expect_tx(bar_x, xbytes);     // next update's x halos
             const double* my_scal = scal + 2 * (int)((it - A.it0) & 1);
             const T ta = (T)my_scal[0], t1a = (T)my_scal[1];
             apc_mbar_wait(bar_r, ph_r);                          // the neighbours' edge values of r are in the halos
             ph_r ^= 1u;
+            APC_TICK(3)
             double s_d = 0.0, s_x = 0.0;
             T g[EPT][C];
 #pragma unroll
@@ -526,6 +536,7 @@ __global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdAr
                 push(lbx, rbx, 0u, reach_a, reach_b, j0 + e, xa[e]);
             }
             psum[tid] = make_double2(s_d, s_x);
+            APC_TICK(4)
         }
         __syncthreads();                                         // B: own part of sx, the sums and `dec` complete; every pass thread is past the wait on bar_r
         if (pending && *dec != 0 && it > A.min_iter) {           // the loop had ended before this update: drop it
@@ -539,7 +550,14 @@ __global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdAr
         t_c = t_n;
         ++it;
         go = it <= A.max_iter || it <= A.min_iter;               // (and the metric above the threshold: known one update later)
+        if (!scalar_warp) APC_TICK(5)
     }
+#ifdef APC_PHASE_TIMING
+    if ((tid == 0 || tid == 64) && (rank == 1 || rank == CL - 1) && it > A.it0)
+        printf("apgd cluster block %d thread %d: %lld updates; cycles per update: wait x %lld, residual pass %lld, barrier A %lld, wait r %lld, "
+               "gradient pass + prox + stores %lld, barrier B + loop %lld\n", rank, tid, it - A.it0, ph[0] / (it - A.it0), ph[1] / (it - A.it0),
+               ph[2] / (it - A.it0), ph[3] / (it - A.it0), ph[4] / (it - A.it0), ph[5] / (it - A.it0));
+#endif
     if (scalar_warp) {
         if (pending) {                                           // the last update's row of diagnostics
             send_sums(it - 1);
