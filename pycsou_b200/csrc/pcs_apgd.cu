@@ -457,7 +457,7 @@ __global__ void __launch_bounds__(APC_BLOCK, 1) apgd_cluster_kernel(const ApgdAr
     long long ph[6] = {0, 0, 0, 0, 0, 0}, tk = clock64();
 #define APC_TICK(i) { const long long now_ = clock64(); ph[i] += now_ - tk; tk = now_; }
 #else
-#define APC_TICK(i)
+#define APC_TICK(i) {}
 #endif
     T xk[EPT], pk[EPT];                                          // pass threads: the state before the update in flight
     bool pending = false;                                        // the sums of update it - 1 have not been looked at yet
@@ -618,7 +618,9 @@ template <typename T, int EPT, int APC_NT> int apgd_cluster_launch(const ApgdArg
 }
 template <typename T> int apgd_cluster_try(const ApgdArgs<T>& A, cudaStream_t s) {
     const char* env = getenv("PCS_APGD_CLUSTER");               // PCS_APGD_CLUSTER=0 keeps the single-block kernel (read per call)
-    if ((env && atoi(env) == 0) || A.n < 2048) return -1;
+    const char* envn = getenv("PCS_APGD_CLUSTER_MIN_N");         // (experiments: smallest n that takes the cluster kernel)
+    const int min_n = envn ? atoi(envn) : 2048;
+    if ((env && atoi(env) == 0) || A.n < min_n) return -1;
     const int nhp = (A.nh + APGD_C - 1) / APGD_C * APGD_C, exw = nhp + APGD_C;
     for (int CL : {16, 8}) {
         const int per = (A.n + CL - 1) / CL;
