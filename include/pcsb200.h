@@ -258,8 +258,8 @@ int pcs_cps_mri_ball_step_c128(void* u_out, void* spec_next, const void* u, cons
 /* ---- a whole AcceleratedProximalGradientDescent solve in one launch: the loop of core/solver.py:55-76 with
  *      update_iterand / update_diagnostics / stopping_metric of opt/proxalgs.py:586-622, for
  *        F = 1/2||h * x - y||^2 (flat Convolve1D, linop/conv.py:20-164), G = none | g_param-threshold L1 | nonneg.
- *   The problem stays in shared memory (n <= pcs_apgd_conv1d_run_max_n(); at most 256 taps): of one block, or -- n >= 2048 on a
- *   device that can place a cluster of 16 or 8 blocks, unless PCS_APGD_CLUSTER=0 -- split over the blocks of one thread-block
+ *   The problem stays in shared memory (n <= pcs_apgd_conv1d_run_max_n(); at most 256 taps): of one block, or -- n >= 512 on a
+ *   device that can place the cluster, unless PCS_APGD_CLUSTER=0 -- split over the 2 to 16 blocks of one thread-block
  *   cluster, which hand edge values to their neighbours through distributed shared memory.  Either way the launch runs
  *   updates it0, it0+1, ... while (it <= max_iter and ||x'-x||/||x|| > threshold) or it <= min_iter, exactly as the reference
  *   does (the cluster kernel starts an update before the sums behind the test are in and drops it if they say stop).

@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(NT, 1) apgd_run_kernel(const ApgdArgs<T> A) {
 
 // ---- the same solve on a CLUSTER of thread blocks --------------------------------------------------------------------------
 // One SM bounds the single-block kernel: at N = 4096 with a 65-tap filter an update is 532 k FP64 multiply-adds = 4.4 us of one
-// SM's FP64 pipe (11.4 us measured).  Here a thread-block cluster (16 blocks, 8 if the device cannot place 16) shares the
+// SM's FP64 pipe (11.4 us measured).  Here a thread-block cluster (2 to 16 blocks, as many as the vector needs) shares the
 // vector: block c owns M = 128 EPT consecutive elements and keeps them (and the residual) in ITS shared memory with a halo
 // on either side.
 // * Neighbours.  The thread that computes an element within the filter's reach of the edge of the segment also stores it
@@ -596,10 +596,10 @@ template <typename T, int EPT, int APC_NT> int apgd_cluster_launch(const ApgdArg
     cfg.attrs = at; cfg.numAttrs = 1;
     // Function attributes and the "can one such cluster be resident" query: once per device, kernel and cluster size
     // (0 not asked yet, 1 yes, -1 no).  A race between host threads only repeats the calls.
-    static signed char ready[64][2];
+    static signed char ready[64][4];
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return -1;
-    signed char& rdy = ready[dev][CL == 16 ? 0 : 1];
+    signed char& rdy = ready[dev][CL == 2 ? 0 : (CL == 4 ? 1 : (CL == 8 ? 2 : 3))];
     if (rdy == 0) {
         int nclusters = 0;
         const bool ok = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess &&
@@ -619,15 +619,18 @@ template <typename T, int EPT, int APC_NT> int apgd_cluster_launch(const ApgdArg
 template <typename T> int apgd_cluster_try(const ApgdArgs<T>& A, cudaStream_t s) {
     const char* env = getenv("PCS_APGD_CLUSTER");               // PCS_APGD_CLUSTER=0 keeps the single-block kernel (read per call)
     const char* envn = getenv("PCS_APGD_CLUSTER_MIN_N");         // (experiments: smallest n that takes the cluster kernel)
-    const int min_n = envn ? atoi(envn) : 2048;
+    // An update of the cluster kernel costs about the same 1.9-2.3 us (fp64) whatever n: it wins from n = 512 on (single
+    // block: 2.7 us there, 4.0 at 1024, 6.6 at 2047, 11.4 at 4096; profiles/r02_apgd_cluster.txt).
+    const int min_n = envn ? atoi(envn) : 512;
     if ((env && atoi(env) == 0) || A.n < min_n) return -1;
     const int nhp = (A.nh + APGD_C - 1) / APGD_C * APGD_C, exw = nhp + APGD_C;
-    for (int CL : {16, 8}) {
-        const int per = (A.n + CL - 1) / CL;
-        const int ept = per <= 2 * 128 ? 2 : (per <= 4 * 128 ? 4 : 0);      // elements per thread: even (pair-aligned windows)
-        if (ept == 0 || 128 * ept < exw) continue;
-        const int rc = ept == 2 ? apgd_cluster_launch<T, 2, 128>(A, CL, s) : apgd_cluster_launch<T, 4, 128>(A, CL, s);
-        if (rc != -1) return rc;
+    // the smallest cluster that holds the vector at 2 elements per thread, else at 4
+    for (int ept : {2, 4}) {
+        for (int CL : {2, 4, 8, 16}) {
+            if ((int64_t)CL * 128 * ept < A.n || 128 * ept < exw) continue;
+            const int rc = ept == 2 ? apgd_cluster_launch<T, 2, 128>(A, CL, s) : apgd_cluster_launch<T, 4, 128>(A, CL, s);
+            if (rc != -1) return rc;
+        }
     }
     return -1;
 }

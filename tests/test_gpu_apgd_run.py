@@ -106,17 +106,19 @@ def _solve(cluster, *a, **kw):
 
 @pytest.mark.parametrize('n,nh,gname,acc', [(4096, 65, 'l1', 'CD'), (4096, 64, 'l1', 'BT'), (2048, 33, 'nonneg', None),
                                             (2049, 9, 'none', 'BT'), (8191, 255, 'l1', 'CD'), (3000, 1, 'l1', 'CD'),
-                                            (6000, 200, 'nonneg', 'CD'), (8192, 129, 'l1', 'CD')])
+                                            (6000, 200, 'nonneg', 'CD'), (8192, 129, 'l1', 'CD'), (512, 33, 'l1', 'CD'),
+                                            (600, 255, 'l1', 'BT'), (1024, 64, 'nonneg', 'CD'), (1500, 129, 'l1', 'CD')])
 @pytest.mark.parametrize('dtype', ['float64', 'float32'])
 def test_cluster_kernel_equals_single_block_kernel(n, nh, gname, acc, dtype):
-    """The thread-block-cluster kernel (n >= 2048) against the single-block one: same number of updates under the live
+    """The thread-block-cluster kernel (n >= 512) against the single-block one: same number of updates under the live
     stop test (the cluster kernel starts an update before the sums of the previous one are in and drops it if they say
     stop), same diagnostics, iterates equal up to the order in which the taps are added."""
     kw = dict(max_iter=300, min_iter=5, accuracy_threshold=3e-3, dtype=dtype)
     s0, e0, r0, L0, _ = _solve(False, n, nh, gname, acc, **kw)
     s1, e1, r1, L1, _ = _solve(True, n, nh, gname, acc, **kw)
     assert L0['kernel'] == 'apgd_run_kernel' and L0['blocks'] == 1
-    assert L1['kernel'] == 'apgd_cluster_kernel' and L1['blocks'] in (8, 16) and L1['threads'] == 160
+    assert L1['kernel'] == 'apgd_cluster_kernel' and L1['threads'] == 160
+    assert L1['blocks'] in (2, 4, 8, 16) and L1['blocks'] * 128 * L1['per_thread'] >= n          # the smallest cluster that holds n
     assert s0.iter == s1.iter and e0['past_t'] == e1['past_t'] and len(r0) == len(r1)
     tol = 1e-12 if dtype == 'float64' else 1e-4
     assert rel_l2(e1['iterand'], e0['iterand']) < tol and rel_l2(e1['past_aux'], e0['past_aux']) < tol
