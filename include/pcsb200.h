@@ -186,7 +186,8 @@ int pcs_mask_to_indices_static(const void* mask_u8, int64_t n, void* total_out_i
  *   strip_cols / nseg: launch geometry overrides (0 = automatic).  use_tma: 0 plain staging, 1 TMA when the image is
  *   16-byte aligned, 2 require TMA, 3 require TMA and the single-role kernel (deconvolution otherwise runs the
  *   warp-specialised one).  diag_out_f64[4] = ||x'-x||^2, ||x||^2, ||z'-z||^2, ||z||^2 (deterministic).
- *   workspace: pcs_pds_tv_workspace_bytes() bytes, zero-initialised once. */
+ *   workspace: pcs_pds_tv_workspace_bytes() bytes (about 23 MB: partial sums, counters and the 21 MB side buffer through
+ *   which the blocks of the on-chip resident kernel hand their boundary rows to their neighbours), zero-initialised once. */
 int64_t pcs_pds_tv_workspace_bytes(void);
 /* What the last pcs_pds_tv_step / _run / _step_slab call of the calling host thread launched (HOST int64[8]):
  * {kernel (0 single-role, 1 warp-specialised with two roles, 2 persistent multi-update, 3 on-chip resident, 4 warp-specialised
